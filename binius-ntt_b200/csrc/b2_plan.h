@@ -1,0 +1,123 @@
+// b2_plan.h -- host-side plan of an additive NTT: domain constants, twiddle classes, per-lane
+// twiddle words and the pass schedule.  Pure C++ (no CUDA calls) so the plan logic is unit-tested
+// on the CPU; b2ntt.cu owns the device side.
+//
+// Reference counterparts: AdditiveNTTConf validation (ntt/nttconf.cuh:55-60),
+// precompute_subspace_evals (ntt/additive_ntt.cuh:273-309), and the launch-shape derivation
+// (ntt/nttconf.cuh:65-110, ntt/nttconf.cu) which this schedule replaces.
+#pragma once
+#include <stdint.h>
+#include <string.h>
+
+#include <vector>
+
+#include "b2_pass.cuh"
+
+namespace b2 {
+
+struct PassDesc {
+	int q0;       // first line bit
+	int k;        // line bits fused
+	int in_line;  // run the in-line layers in this pass
+};
+
+struct HostPlan {
+	int field_bits = 0, layout = 0, log_h = 0, log_rate = 0, batch = 1;
+	int limbs_log = 0;   // 0 or 2
+	int n_inline = 0, lane_shift = 0, batch_bits = 0, sliced_io = 0;
+	int nb = 0;          // line bits per row
+	bool tiny = false;   // fewer than two lines of butterfly work per row: element-wise kernels
+	uint32_t consts[32 * kConstPitch];
+	uint32_t lane_tw[5 * 32];
+	uint8_t cls[32];
+	std::vector<PassDesc> passes;  // in forward execution order (highest line bits first)
+};
+
+inline bool plan_args_ok(int field_bits, int layout, int log_h, int log_rate, int batch) {
+	if (field_bits != 32 && field_bits != 128) return false;
+	if (layout != 0 && layout != 1) return false;
+	if (log_h < 1 || log_rate < 0 || log_rate > 4 || log_h + log_rate > 32) return false;  // nttconf.cuh:55-60
+	if (layout == 1 && log_h < 5) return false;  // a bit-sliced block is 32 elements
+	if (batch < 1) return false;
+	return true;
+}
+
+// normalised subspace-polynomial evaluations C[i][j] = W^_i(beta_{i+1+j}), beta_i = 1 << i
+inline void plan_constants(int log_h, int log_rate, uint32_t* C /* [32][kConstPitch] */) {
+	memset(C, 0, sizeof(uint32_t) * 32 * kConstPitch);
+	uint32_t norm[32];
+	const int width = log_h + log_rate;
+	for (int i = 1; i < width; i++) C[i - 1] = uint32_t(1) << i;
+	norm[0] = 1;
+	for (int i = 1; i < log_h; i++) {
+		const uint32_t* prev = C + (i - 1) * kConstPitch;
+		uint32_t* row = C + i * kConstPitch;
+		const uint32_t np = norm[i - 1];
+		// subspace map e -> e^2 + norm * e (additive_ntt.cuh:16-19)
+		norm[i] = gf32_square(prev[0]) ^ gf32_mul(np, prev[0]);
+		for (int j = 1; j < width - i; j++) row[j - 1] = gf32_square(prev[j]) ^ gf32_mul(np, prev[j]);
+	}
+	for (int i = 0; i < log_h; i++) {
+		const uint32_t inv = gf32_inverse(norm[i]);
+		uint32_t* row = C + i * kConstPitch;
+		for (int j = 0; j < width - i - 1; j++) row[j] = gf32_mul(inv, row[j]);
+	}
+}
+
+inline int twiddle_class(uint32_t or_of_values) {
+	if (or_of_values == 0) return 0;
+	if (or_of_values < (1u << 4)) return 2;
+	if (or_of_values < (1u << 8)) return 3;
+	if (or_of_values < (1u << 16)) return 4;
+	return 5;
+}
+
+inline int plan_build(HostPlan& hp, int field_bits, int layout, int log_h, int log_rate, int batch) {
+	if (!plan_args_ok(field_bits, layout, log_h, log_rate, batch)) return -1;
+	hp.field_bits = field_bits, hp.layout = layout, hp.log_h = log_h, hp.log_rate = log_rate, hp.batch = batch;
+	hp.limbs_log = field_bits == 128 ? 2 : 0;
+	if (layout == 0) {
+		hp.n_inline = 5 - hp.limbs_log, hp.lane_shift = hp.limbs_log, hp.batch_bits = 0, hp.sliced_io = 0;
+	} else {
+		hp.n_inline = 5, hp.lane_shift = 0, hp.batch_bits = hp.limbs_log, hp.sliced_io = 1;
+	}
+	hp.nb = log_h + hp.limbs_log - 5;
+	plan_constants(log_h, log_rate, hp.consts);
+	for (int s = 0; s < 32; s++) {
+		uint32_t m = 0;
+		for (int b = 0; b < kConstPitch; b++) m |= hp.consts[s * kConstPitch + b];
+		hp.cls[s] = (uint8_t)twiddle_class(m);
+	}
+	memset(hp.lane_tw, 0, sizeof hp.lane_tw);
+	for (int s = 0; s < hp.n_inline && s < log_h; s++)
+		for (int x = 0; x < 32; x++) {
+			const uint32_t y = (uint32_t)x >> (s + hp.lane_shift + 1);
+			uint32_t val = 0;
+			for (int b = 0; (y >> b) != 0; b++)
+				if ((y >> b) & 1) val ^= hp.consts[s * kConstPitch + b];
+			for (int i = 0; i < 32; i++) hp.lane_tw[s * 32 + i] |= ((val >> i) & 1u) << x;
+		}
+	const int nbf = hp.nb - hp.batch_bits;  // butterfly line bits
+	hp.passes.clear();
+	hp.tiny = nbf < 1;
+	if (!hp.tiny) {
+		const int np = (nbf + kMaxPassBits - 1) / kMaxPassBits;
+		// the lowest pass also runs the in-line layers, so it gets the smallest share of line bits
+		int left = nbf;
+		std::vector<int> ks(np);
+		for (int p = np - 1; p >= 0; p--) {  // p = np-1 is the highest pass
+			int share = (left + p) / (p + 1);
+			ks[p] = share;
+			left -= share;
+		}
+		// ks[0] lowest ... ks[np-1] highest; emit highest first
+		int q = hp.batch_bits + nbf;
+		for (int p = np - 1; p >= 0; p--) {
+			q -= ks[p];
+			hp.passes.push_back(PassDesc{q, ks[p], p == 0 ? 1 : 0});
+		}
+	}
+	return 0;
+}
+
+}  // namespace b2

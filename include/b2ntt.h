@@ -1,0 +1,104 @@
+/*
+ * b2ntt.h -- C ABI of the B200 (sm_100a) additive-NTT / tower-field library (libb2ntt.so).
+ *
+ * This is the drop-in boundary for the hot path of shourovrm/binius-NTT.  The reference exposes
+ * the path as C++ header templates plus a handful of compiled symbols (there is no FFI in the
+ * reference); each entry point below names the reference interface it replaces, paths relative to
+ * /root/reference/src/ulvt/.  The thin C++ shims in include/ulvt/ keep the reference's own class
+ * names on top of these calls.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no C++ or torch types cross this boundary.
+ *   - every function returns 0 (B2NTT_OK) or a negative B2NTT_E* code; nothing aborts or throws.
+ *   - "d_" pointers are device pointers on the plan's device, "h_" pointers are host pointers.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream); device entry
+ *     points are asynchronous on that stream.
+ *   - GF(2^32) element = uint32_t; GF(2^128) element = four little-endian uint32_t limbs
+ *     (README.md:43).  Bit-sliced layout = blocks of 32 consecutive elements, `width_bits` words
+ *     per block, word 32*limb + b = bit b of that limb of the 32 elements (utils/bitslicing.cuh:32-47).
+ *   - there is NO CPU fallback: without a CUDA device every compute entry point returns B2NTT_ECUDA.
+ */
+#ifndef B2NTT_H
+#define B2NTT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+	B2NTT_OK = 0,
+	B2NTT_EINVAL = -1,       /* bad argument (what makes AdditiveNTT::apply return false / ASSERT fire) */
+	B2NTT_ENOMEM = -2,       /* host or device allocation failed */
+	B2NTT_ECUDA = -3,        /* CUDA runtime error or no usable device */
+	B2NTT_EUNSUPPORTED = -4  /* valid request this build does not implement */
+};
+
+enum { B2NTT_LAYOUT_COMPACT = 0, B2NTT_LAYOUT_BITSLICED = 1 };
+
+typedef struct b2ntt_plan b2ntt_plan;
+
+/* Replaces AdditiveNTTConf<T,P>(log_h, log_rate) + AdditiveNTT<T,P>(conf)
+ * (ntt/nttconf.cuh:49-60, ntt/additive_ntt.cuh:178-199): validates the configuration
+ * (1 <= log_h, 0 <= log_rate <= 4, log_h + log_rate <= 32), builds the domain constants
+ * (precompute_subspace_evals, additive_ntt.cuh:273-309, basis beta_i = 1 << i) and the pass schedule.
+ *   field_bits  32 or 128
+ *   layout      B2NTT_LAYOUT_COMPACT or B2NTT_LAYOUT_BITSLICED (input and output images)
+ *   batch       number of independent columns transformed per call (>= 1); column b reads
+ *               in[b * 2^log_h ...] and writes out[b * 2^(log_h+log_rate) ...]
+ *   device      CUDA device ordinal */
+int b2ntt_plan_create(b2ntt_plan** plan, int field_bits, int layout, int log_h, int log_rate, int batch, int device);
+int b2ntt_plan_destroy(b2ntt_plan* plan);
+
+/* Replaces the kernel launch loop of AdditiveNTT::apply (additive_ntt.cuh:222-247) on data that is
+ * already in device memory.  d_in: batch * 2^log_h elements (novel-basis coefficients, natural order);
+ * d_out: batch * 2^(log_h+log_rate) elements, coset-major per column: out[c * 2^log_h + i]
+ * (additive_ntt.cuh:250-259).  d_out may equal d_in when log_rate == 0. */
+int b2ntt_exec(b2ntt_plan* plan, const void* d_in, void* d_out, void* stream);
+
+/* Inverse of b2ntt_exec on ONE coset per column (no reference counterpart):
+ * d_in = batch * 2^log_h evaluations on coset `coset`, d_out = batch * 2^log_h coefficients. */
+int b2ntt_exec_inverse(b2ntt_plan* plan, const void* d_in, void* d_out, int coset, void* stream);
+
+/* Replaces bool AdditiveNTT::apply(const NTTData&, NTTData&) (additive_ntt.cuh:201-265): host input,
+ * host output, H2D + transform + D2H + synchronise on the plan's own stream.  n_in is the input
+ * element count per column and must equal 2^log_h (else B2NTT_EINVAL, apply()'s `return false`). */
+int b2ntt_exec_host(b2ntt_plan* plan, const void* h_in, size_t n_in, void* h_out);
+
+/* Query: number of kernel launches one b2ntt_exec issues, and HBM passes over the data set. */
+int b2ntt_plan_launches(const b2ntt_plan* plan);
+int b2ntt_plan_passes(const b2ntt_plan* plan);
+/* Copies the plan's normalised domain constants C[i][j] (row pitch 32 words, 32 rows) to h_out. */
+int b2ntt_plan_constants(const b2ntt_plan* plan, uint32_t* h_out);
+
+/* Replaces transpose_kernel<W> / untranspose_kernel<W> (utils/bitslicing.cuh:89-104), in place on
+ * n_blocks blocks of 32 elements.  width_bits 32, 64 or 128.  dir 0: compact -> bit-sliced,
+ * 1: bit-sliced -> compact. */
+int b2ntt_bitslice(void* d_buf, size_t n_blocks, int width_bits, int dir, void* stream);
+
+/* Element-wise tower product out[i] = a[i] * b[i], n elements.
+ *   compact   field_bits 8/16/32 (one element per uint32_t, FanPaarTowerField<H>::multiply,
+ *             finite_fields/binary_tower.cuh:113-115) or 128 (4 limbs, sumcheck/test/utils/tower_7_mul.cu:4-20)
+ *   bitsliced field_bits 32 or 128, n a multiple of 32 (multiply_unrolled<5|7>,
+ *             finite_fields/circuit_generator/unrolled/binary_tower_unrolled.cuh:4-5)
+ * d_out may alias d_a or d_b. */
+int b2ntt_mul(int field_bits, int layout, const void* d_a, const void* d_b, void* d_out, size_t n, void* stream);
+
+/* Dependent-chain bit-sliced multiply microbenchmark: every thread squares-and-multiplies `iters`
+ * times in registers (the shape of bitsliced_repeat, finite_fields/tests/profiling/kernels/
+ * bitsliced_repeat.cu:6-33).  Used to measure the logic-pipe peak.  d_io: threads * 2^h words. */
+int b2ntt_mul_repeat(int field_bits, void* d_io, size_t n_threads, int iters, void* stream);
+
+/* Replaces bool check_gpu_capabilities() (utils/common.cu:6-43): 1 capable, 0 not, <0 error. */
+int b2ntt_check_gpu_capabilities(int device);
+
+const char* b2ntt_strerror(int code);
+/* Text of the last CUDA error seen by the calling thread's last failing call ("" if none). */
+const char* b2ntt_last_cuda_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
