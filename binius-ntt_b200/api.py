@@ -1,0 +1,228 @@
+"""ctypes binding of libb2ntt.so and the reference-shaped host classes on top of it."""
+import ctypes as C
+import enum
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LAYOUT_COMPACT, LAYOUT_BITSLICED = 0, 1
+
+_lib = None
+
+
+class B2NTTError(RuntimeError):
+    def __init__(self, code, where):
+        self.code = code
+        msg = lib().b2ntt_strerror(code).decode()
+        cuda = lib().b2ntt_last_cuda_error().decode()
+        super().__init__(f"{where}: {msg} ({code})" + (f" [{cuda}]" if cuda and code == -3 else ""))
+
+
+def lib_path():
+    return os.path.join(HERE, "libb2ntt.so")
+
+
+def lib():
+    """The product library.  Raises if it was not built: there is no other compute path."""
+    global _lib
+    if _lib is None:
+        p = lib_path()
+        if not os.path.exists(p):
+            raise ImportError(f"{p} is missing: build it with `make -C binius-ntt_b200/csrc` (or __graft_entry__.build())")
+        L = C.CDLL(p)
+        vp, i, sz = C.c_void_p, C.c_int, C.c_size_t
+        L.b2ntt_plan_create.argtypes = [C.POINTER(vp), i, i, i, i, i, i]
+        L.b2ntt_plan_destroy.argtypes = [vp]
+        L.b2ntt_exec.argtypes = [vp, vp, vp, vp]
+        L.b2ntt_exec_inverse.argtypes = [vp, vp, vp, i, vp]
+        L.b2ntt_exec_host.argtypes = [vp, vp, sz, vp]
+        L.b2ntt_plan_launches.argtypes = [vp]
+        L.b2ntt_plan_passes.argtypes = [vp]
+        L.b2ntt_plan_constants.argtypes = [vp, vp]
+        L.b2ntt_bitslice.argtypes = [vp, sz, i, i, vp]
+        L.b2ntt_mul.argtypes = [i, i, vp, vp, vp, sz, vp]
+        L.b2ntt_mul_repeat.argtypes = [i, vp, sz, i, vp]
+        L.b2ntt_check_gpu_capabilities.argtypes = [i]
+        L.b2ntt_strerror.argtypes = [i]
+        L.b2ntt_strerror.restype = C.c_char_p
+        L.b2ntt_last_cuda_error.restype = C.c_char_p
+        _lib = L
+    return _lib
+
+
+def _check(rc, where):
+    if rc != 0:
+        raise B2NTTError(rc, where)
+
+
+def _stream_ptr(stream):
+    if stream is None:
+        import torch
+
+        return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    if isinstance(stream, int):
+        return C.c_void_p(stream)
+    return C.c_void_p(stream.cuda_stream)
+
+
+class Plan:
+    """b2ntt_plan: domain constants + pass schedule for (field, layout, log_h, log_rate, batch)."""
+
+    def __init__(self, field_bits, log_h, log_rate=0, layout=LAYOUT_COMPACT, batch=1, device=0):
+        self._h = C.c_void_p()
+        _check(lib().b2ntt_plan_create(C.byref(self._h), field_bits, layout, log_h, log_rate, batch, device), "b2ntt_plan_create")
+        self.field_bits, self.log_h, self.log_rate, self.layout, self.batch, self.device = field_bits, log_h, log_rate, layout, batch, device
+        self.limbs = field_bits // 32
+        self.in_words = (batch << log_h) * self.limbs
+        self.out_words = self.in_words << log_rate
+
+    def close(self):
+        if self._h:
+            lib().b2ntt_plan_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def launches(self):
+        return lib().b2ntt_plan_launches(self._h)
+
+    @property
+    def passes(self):
+        return lib().b2ntt_plan_passes(self._h)
+
+    def constants(self):
+        out = np.zeros((32, 32), dtype=np.uint32)
+        _check(lib().b2ntt_plan_constants(self._h, out.ctypes.data), "b2ntt_plan_constants")
+        return out
+
+    def _dev_ok(self, t, words, name):
+        import torch
+
+        if not (t.is_cuda and t.is_contiguous() and t.dtype in (torch.int32, torch.uint32)):
+            raise ValueError(f"{name}: need a contiguous CUDA int32/uint32 tensor")
+        if t.numel() != words:
+            raise ValueError(f"{name}: expected {words} words, got {t.numel()}")
+
+    def exec(self, d_in, d_out=None, stream=None):
+        """Forward transform of device tensors (32-bit words).  Returns d_out."""
+        import torch
+
+        self._dev_ok(d_in, self.in_words, "d_in")
+        if d_out is None:
+            d_out = d_in if self.log_rate == 0 else torch.empty(self.out_words, dtype=d_in.dtype, device=d_in.device)
+        self._dev_ok(d_out, self.out_words, "d_out")
+        _check(lib().b2ntt_exec(self._h, d_in.data_ptr(), d_out.data_ptr(), _stream_ptr(stream)), "b2ntt_exec")
+        return d_out
+
+    def exec_inverse(self, d_in, d_out=None, coset=0, stream=None):
+        self._dev_ok(d_in, self.in_words, "d_in")
+        if d_out is None:
+            d_out = d_in
+        self._dev_ok(d_out, self.in_words, "d_out")
+        _check(lib().b2ntt_exec_inverse(self._h, d_in.data_ptr(), d_out.data_ptr(), coset, _stream_ptr(stream)), "b2ntt_exec_inverse")
+        return d_out
+
+    def exec_host(self, h_in, h_out=None):
+        """Host numpy (or pinned torch CPU tensor) in -> host out: H2D + transform + D2H + sync."""
+        a = _host_words(h_in)
+        if h_out is None:
+            h_out = np.empty(self.out_words, dtype=np.uint32)
+        o = _host_words(h_out)
+        if o.size != self.out_words:
+            raise ValueError("h_out: wrong size")
+        n_in = a.size // self.limbs // self.batch if a.size % (self.limbs * self.batch) == 0 else 0
+        _check(lib().b2ntt_exec_host(self._h, a.ctypes.data, n_in, o.ctypes.data), "b2ntt_exec_host")
+        return h_out
+
+
+def _host_words(x):
+    if isinstance(x, np.ndarray):
+        if x.dtype != np.uint32 or not x.flags.c_contiguous:
+            raise ValueError("host buffers must be C-contiguous uint32")
+        return x.reshape(-1)
+    # torch CPU tensor (possibly pinned): view it through numpy without copying
+    return x.view(-1).numpy().view(np.uint32)
+
+
+def bitslice_(d_buf, width_bits, inverse=False, stream=None):
+    """In-place compact <-> bit-sliced conversion of a device tensor (transpose_kernel<W> /
+    untranspose_kernel<W>, utils/bitslicing.cuh:89-104)."""
+    n_blocks, rem = divmod(d_buf.numel(), width_bits)
+    if rem:
+        raise ValueError("buffer is not a whole number of 32-element blocks")
+    _check(lib().b2ntt_bitslice(d_buf.data_ptr(), n_blocks, width_bits, 1 if inverse else 0, _stream_ptr(stream)), "b2ntt_bitslice")
+    return d_buf
+
+
+def mul(a, b, field_bits, layout=LAYOUT_COMPACT, out=None, stream=None):
+    """Element-wise tower product of device tensors of 32-bit words."""
+    import torch
+
+    if out is None:
+        out = torch.empty_like(a)
+    words_per = 4 if field_bits == 128 else 1
+    n = a.numel() // words_per
+    _check(lib().b2ntt_mul(field_bits, layout, a.data_ptr(), b.data_ptr(), out.data_ptr(), n, _stream_ptr(stream)), "b2ntt_mul")
+    return out
+
+
+def mul_repeat(d_io, field_bits, iters, stream=None):
+    n_threads = d_io.numel() // field_bits
+    _check(lib().b2ntt_mul_repeat(field_bits, d_io.data_ptr(), n_threads, iters, _stream_ptr(stream)), "b2ntt_mul_repeat")
+    return d_io
+
+
+def check_gpu_capabilities(device=0):
+    rc = lib().b2ntt_check_gpu_capabilities(device)
+    if rc < 0:
+        raise B2NTTError(rc, "b2ntt_check_gpu_capabilities")
+    return bool(rc)
+
+
+# ---- the reference's own class names (ntt/nttconf.cuh, ntt/additive_ntt.cuh) -------------------------
+class DataOrder(enum.Enum):
+    IN_ORDER = 0
+    BIT_REVERSED = 1
+
+
+class NTTData:
+    """NTTData<E> (ntt/nttconf.cuh:11-21): host buffer + size + order tag."""
+
+    def __init__(self, order=DataOrder.IN_ORDER, size=0, limbs=1):
+        self.order, self.size, self.limbs = order, size, limbs
+        self.data = np.zeros(size * limbs, dtype=np.uint32)
+
+
+class AdditiveNTTConf:
+    """AdditiveNTTConf<T,P>(log_h, log_rate) (ntt/nttconf.cuh:49-60).  field_bits 32 = (uint32_t,
+    FanPaarTowerField<5>), 128 = GF(2^128) with four limbs."""
+
+    def __init__(self, log_h, log_rate, field_bits=32):
+        if not (log_h >= 1 and 0 <= log_rate <= 4 and log_h + log_rate <= 32):
+            raise ValueError("AdditiveNTTConf: need 1 <= log_h, 0 <= log_rate <= 4, log_h + log_rate <= 32")
+        self.log_h, self.log_rate, self.field_bits = log_h, log_rate, field_bits
+
+
+class AdditiveNTT:
+    """AdditiveNTT<T,P>(conf) with bool apply(in, out) (ntt/additive_ntt.cuh:178-265)."""
+
+    def __init__(self, conf, device=0):
+        self.conf = conf
+        self.plan = Plan(conf.field_bits, conf.log_h, conf.log_rate, device=device)
+
+    def apply(self, inp, out):
+        if inp.size != (1 << self.conf.log_h) or inp.order != DataOrder.IN_ORDER:
+            return False  # additive_ntt.cuh:206-208
+        n_out = (1 << (self.conf.log_h + self.conf.log_rate)) * self.plan.limbs
+        if out.data.size != n_out:
+            out.data = np.empty(n_out, dtype=np.uint32)
+        out.size = 1 << (self.conf.log_h + self.conf.log_rate)
+        out.order = DataOrder.IN_ORDER
+        self.plan.exec_host(inp.data, out.data)
+        return True

@@ -1,0 +1,33 @@
+// b2_launch.h -- host-callable launchers of the CUDA kernels (one per translation unit), used by
+// the C ABI implementation in b2ntt.cu.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b2 {
+
+struct PassParams;
+
+// element-wise path for transforms with fewer than two 128-byte lines per row
+struct TinyParams {
+	const uint32_t* src;
+	uint32_t* dst;
+	const uint32_t* consts;  // device copy of the [32][kConstPitch] constants
+	int log_h, log_rate, limbs_log;
+	int rows;            // columns x cosets (forward) or columns (inverse)
+	int src_row_shift;   // log_rate on the forward fan-out
+	uint32_t coset_mask;
+	uint32_t coset0;
+	int inverse;
+};
+
+int launch_pass(const PassParams& P, cudaStream_t stream);
+int launch_tiny_fanout(const TinyParams& T, cudaStream_t stream);
+int launch_tiny_layers(const TinyParams& T, cudaStream_t stream);
+
+// b2_misc.cu
+int launch_bitslice(uint32_t* d, uint64_t n_blocks, int width_bits, int dir, cudaStream_t stream);
+int launch_mul(int field_bits, int layout, const uint32_t* a, const uint32_t* b, uint32_t* out, uint64_t n, cudaStream_t stream);
+int launch_mul_repeat(int field_bits, uint32_t* io, uint64_t n_threads, int iters, cudaStream_t stream);
+
+}  // namespace b2

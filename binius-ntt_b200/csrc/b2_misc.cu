@@ -1,0 +1,271 @@
+// b2_misc.cu -- layout conversion and element-wise tower-multiply kernels.  sm_100a only.
+//
+// Replaces transpose_kernel<W> / untranspose_kernel<W> (utils/bitslicing.cuh:89-104), the smoke
+// kernels of finite_fields/tests/test_kernels.cu:9-60 and bitsliced_repeat
+// (finite_fields/tests/profiling/kernels/bitsliced_repeat.cu:6-33).
+#include <cuda_runtime.h>
+
+#include "b2_bundle.cuh"
+#include "b2_launch.h"
+
+namespace b2 {
+
+// ------------------------------------------------------------------------------------------------
+// compact <-> little-endian bit-sliced, blocks of 32 elements of L = width/32 limbs.
+// compact: word e*L + k = limb k of element e; bit-sliced: word 32*k + b = bit b of limb k of the
+// 32 elements, element e at bit position e (utils/bitslicing.cuh:32-47).
+// A warp converts 32 blocks at a time through shared memory so that global accesses are whole
+// 128-byte lines; each thread transposes one (block, limb) 32x32 bit matrix in registers.
+// ------------------------------------------------------------------------------------------------
+template <int L>
+__global__ void __launch_bounds__(128) bitslice_kernel(uint32_t* __restrict__ d, uint64_t n_blocks, int dir) {
+	constexpr int W = 32 * L;               // words per block
+	__shared__ uint32_t sm[4][32 * 33];     // per warp: 32 lines of 32 words, padded
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	uint32_t* s = sm[warp];
+	// a "unit" = one (block, limb) matrix; units of a block are contiguous in the sliced image only
+	const uint64_t n_groups = (n_blocks * L + 31) / 32;  // groups of 32 units (= 32/L blocks)
+	for (uint64_t grp = (uint64_t)blockIdx.x * 4 + warp; grp < n_groups; grp += (uint64_t)gridDim.x * 4) {
+		// 32/L blocks x W words = 1024 words, contiguous in memory
+		const uint64_t base = grp * 1024;
+		const uint64_t total = n_blocks * W;
+		uint32_t r[32];
+		// coalesced load of 32 lines into shared memory (line i, word lane)
+#pragma unroll
+		for (int i = 0; i < 32; i++) {
+			const uint64_t g = base + (uint64_t)i * 32 + lane;
+			s[i * 33 + lane] = g < total ? d[g] : 0u;
+		}
+		__syncwarp();
+		// unit = lane: block lb = lane / L, limb k = lane % L
+		const int lb = lane / L, k = lane % L;
+		if (dir == 0) {
+			// gather limb k of elements 0..31 of block lb: compact word (e*L + k) of the block
+#pragma unroll
+			for (int e = 0; e < 32; e++) {
+				const int wi = lb * W + e * L + k;
+				r[e] = s[(wi >> 5) * 33 + (wi & 31)];
+			}
+		} else {
+#pragma unroll
+			for (int b = 0; b < 32; b++) {
+				const int wi = lb * W + 32 * k + b;
+				r[b] = s[(wi >> 5) * 33 + (wi & 31)];
+			}
+		}
+		transpose32(r);
+		__syncwarp();
+		if (dir == 0) {
+#pragma unroll
+			for (int b = 0; b < 32; b++) {
+				const int wi = lb * W + 32 * k + b;
+				s[(wi >> 5) * 33 + (wi & 31)] = r[b];
+			}
+		} else {
+#pragma unroll
+			for (int e = 0; e < 32; e++) {
+				const int wi = lb * W + e * L + k;
+				s[(wi >> 5) * 33 + (wi & 31)] = r[e];
+			}
+		}
+		__syncwarp();
+#pragma unroll
+		for (int i = 0; i < 32; i++) {
+			const uint64_t g = base + (uint64_t)i * 32 + lane;
+			if (g < total) d[g] = s[i * 33 + lane];
+		}
+		__syncwarp();
+	}
+}
+
+int launch_bitslice(uint32_t* d, uint64_t n_blocks, int width_bits, int dir, cudaStream_t stream) {
+	if (n_blocks == 0) return 0;
+	const int L = width_bits / 32;
+	const uint64_t n_groups = (n_blocks * L + 31) / 32;
+	unsigned blocks = (unsigned)((n_groups + 3) / 4);
+	if (blocks > 148 * 16) blocks = 148 * 16;
+	switch (L) {
+		case 1: bitslice_kernel<1><<<blocks, 128, 0, stream>>>(d, n_blocks, dir); break;
+		case 2: bitslice_kernel<2><<<blocks, 128, 0, stream>>>(d, n_blocks, dir); break;
+		case 4: bitslice_kernel<4><<<blocks, 128, 0, stream>>>(d, n_blocks, dir); break;
+		default: return -1;
+	}
+	return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
+// ------------------------------------------------------------------------------------------------
+// element-wise products
+// ------------------------------------------------------------------------------------------------
+template <int H>
+__global__ void mul_compact_kernel(const uint32_t* __restrict__ a, const uint32_t* __restrict__ b, uint32_t* __restrict__ o, uint64_t n) {
+	for (uint64_t g = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; g < n; g += (uint64_t)gridDim.x * blockDim.x)
+		o[g] = (uint32_t)Tower<H>::mul(a[g], b[g]);
+}
+
+__global__ void mul_compact128_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, uint4* __restrict__ o, uint64_t n) {
+	for (uint64_t g = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; g < n; g += (uint64_t)gridDim.x * blockDim.x) {
+		const uint4 x = a[g], y = b[g];
+		gf128 p, q;
+		p.w[0] = x.x, p.w[1] = x.y, p.w[2] = x.z, p.w[3] = x.w;
+		q.w[0] = y.x, q.w[1] = y.y, q.w[2] = y.z, q.w[3] = y.w;
+		const gf128 z = gf128_mul(p, q);
+		o[g] = make_uint4(z.w[0], z.w[1], z.w[2], z.w[3]);
+	}
+}
+
+// bit-sliced GF(2^32): one thread per block of 32 products, everything in registers
+__global__ void __launch_bounds__(128) mul_sliced32_kernel(const uint32_t* __restrict__ a, const uint32_t* __restrict__ b, uint32_t* __restrict__ o, uint64_t n_blocks) {
+	for (uint64_t g = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; g < n_blocks; g += (uint64_t)gridDim.x * blockDim.x) {
+		uint32_t x[32], y[32], z[32];
+		const uint4* pa = reinterpret_cast<const uint4*>(a + g * 32);
+		const uint4* pb = reinterpret_cast<const uint4*>(b + g * 32);
+#pragma unroll
+		for (int i = 0; i < 8; i++) {
+			const uint4 u = pa[i], v = pb[i];
+			x[4 * i] = u.x, x[4 * i + 1] = u.y, x[4 * i + 2] = u.z, x[4 * i + 3] = u.w;
+			y[4 * i] = v.x, y[4 * i + 1] = v.y, y[4 * i + 2] = v.z, y[4 * i + 3] = v.w;
+		}
+		Sliced<5>::mul(x, y, z);
+		uint4* po = reinterpret_cast<uint4*>(o + g * 32);
+#pragma unroll
+		for (int i = 0; i < 8; i++) po[i] = make_uint4(z[4 * i], z[4 * i + 1], z[4 * i + 2], z[4 * i + 3]);
+	}
+}
+
+// bit-sliced GF(2^128): a block is 4 limbs x 32 words.  Two Karatsuba levels above GF(2^32) give
+// nine GF(2^32) products; FOUR threads share one block so that each holds at most one 32-word
+// operand pair plus accumulators.  Thread q of the quad computes the products of one GF(2^64)
+// sub-problem and the quad combines through shared memory.
+//   A = (A0, A1), A0 = (a0, a1), A1 = (a2, a3) over GF(2^64); the three GF(2^64) products
+//   Z0 = A0*B0, Z2 = A1*B1, ZZ = (A0+A1)*(B0+B1) go to threads 0..2 (thread 3 helps with stores).
+__device__ __forceinline__ void load32(const uint32_t* p, uint32_t* w) {
+	const uint4* q = reinterpret_cast<const uint4*>(p);
+#pragma unroll
+	for (int i = 0; i < 8; i++) {
+		const uint4 u = q[i];
+		w[4 * i] = u.x, w[4 * i + 1] = u.y, w[4 * i + 2] = u.z, w[4 * i + 3] = u.w;
+	}
+}
+
+// GF(2^64) product of (x0,x1)*(y0,y1) given as 32-word halves read through `ld` from two sources
+// (the operand is src0[limb] ^ src1[limb] when two = true).  out: 64 words.
+__device__ __forceinline__ void sliced64_mul_from(const uint32_t* a0p, const uint32_t* a1p, const uint32_t* b0p, const uint32_t* b1p,
+                                                  bool two, int limb0, uint32_t* out /*64*/) {
+	uint32_t x[32], y[32], t[32], z0[32], z2[32];
+	auto ld = [&](const uint32_t* p0, const uint32_t* p1, int limb, uint32_t* w) {
+		load32(p0 + 32 * limb, w);
+		if (two) {
+			uint32_t u[32];
+			load32(p1 + 32 * limb, u);
+#pragma unroll
+			for (int i = 0; i < 32; i++) w[i] ^= u[i];
+		}
+	};
+	ld(a0p, a1p, limb0, x), ld(b0p, b1p, limb0, y);
+	Sliced<5>::mul(x, y, z0);
+	ld(a0p, a1p, limb0 + 1, t);
+#pragma unroll
+	for (int i = 0; i < 32; i++) x[i] ^= t[i];
+	ld(b0p, b1p, limb0 + 1, t);
+#pragma unroll
+	for (int i = 0; i < 32; i++) y[i] ^= t[i];
+	Sliced<5>::mul(x, y, out + 32);  // zz
+	ld(a0p, a1p, limb0 + 1, x), ld(b0p, b1p, limb0 + 1, y);
+	Sliced<5>::mul(x, y, z2);
+	Sliced<5>::mul_alpha(z2, t);
+#pragma unroll
+	for (int i = 0; i < 32; i++) {
+		const uint32_t lo = z0[i] ^ z2[i];
+		out[i] = lo;
+		out[32 + i] ^= lo ^ t[i];
+	}
+}
+
+__global__ void __launch_bounds__(96) mul_sliced128_kernel(const uint32_t* __restrict__ a, const uint32_t* __restrict__ b, uint32_t* __restrict__ o, uint64_t n_blocks) {
+	// 96 threads = 32 blocks x 3 sub-products; thread (blk, q): q = threadIdx.x / 32
+	__shared__ uint32_t sm[3][32][65];
+	const int q = threadIdx.x >> 5, lb = threadIdx.x & 31;
+	for (uint64_t g0 = (uint64_t)blockIdx.x * 32; g0 < n_blocks; g0 += (uint64_t)gridDim.x * 32) {
+		const uint64_t g = g0 + lb;
+		const bool act = g < n_blocks;
+		uint32_t r[64];
+		if (act) {
+			const uint32_t *pa = a + g * 128, *pb = b + g * 128;
+			if (q == 0) sliced64_mul_from(pa, pa, pb, pb, false, 0, r);        // Z0 = A0*B0
+			else if (q == 1) sliced64_mul_from(pa, pa, pb, pb, false, 2, r);   // Z2 = A1*B1
+			else sliced64_mul_from(pa, pa + 64, pb, pb + 64, true, 0, r);      // ZZ = (A0+A1)*(B0+B1)
+#pragma unroll
+			for (int i = 0; i < 64; i++) sm[q][lb][i] = r[i];
+		}
+		__syncthreads();
+		if (act) {
+			// lo = Z0 + Z2 ; hi = ZZ + Z0 + Z2 + alpha6 * Z2 ; each thread writes a third of the words
+			uint32_t* po = o + g * 128;
+			if (q == 0) {
+				for (int i = 0; i < 64; i++) po[i] = sm[0][lb][i] ^ sm[1][lb][i];
+			} else if (q == 1) {
+				uint32_t z2[64], az[64];
+				for (int i = 0; i < 64; i++) z2[i] = sm[1][lb][i];
+				Sliced<6>::mul_alpha(z2, az);
+				for (int i = 0; i < 64; i++) po[64 + i] = sm[2][lb][i] ^ sm[0][lb][i] ^ z2[i] ^ az[i];
+			}
+		}
+		__syncthreads();
+	}
+}
+
+int launch_mul(int field_bits, int layout, const uint32_t* a, const uint32_t* b, uint32_t* o, uint64_t n, cudaStream_t stream) {
+	if (n == 0) return 0;
+	const unsigned cap = 148 * 16;
+	if (layout == 0) {
+		unsigned blocks = (unsigned)((n + 255) / 256);
+		if (blocks > cap) blocks = cap;
+		switch (field_bits) {
+			case 8: mul_compact_kernel<3><<<blocks, 256, 0, stream>>>(a, b, o, n); break;
+			case 16: mul_compact_kernel<4><<<blocks, 256, 0, stream>>>(a, b, o, n); break;
+			case 32: mul_compact_kernel<5><<<blocks, 256, 0, stream>>>(a, b, o, n); break;
+			case 128:
+				mul_compact128_kernel<<<blocks, 256, 0, stream>>>((const uint4*)a, (const uint4*)b, (uint4*)o, n);
+				break;
+			default: return -1;
+		}
+	} else {
+		if (n % 32) return -1;
+		const uint64_t nb = n / 32;
+		if (field_bits == 32) {
+			unsigned blocks = (unsigned)((nb + 127) / 128);
+			if (blocks > cap) blocks = cap;
+			mul_sliced32_kernel<<<blocks, 128, 0, stream>>>(a, b, o, nb);
+		} else if (field_bits == 128) {
+			unsigned blocks = (unsigned)((nb + 31) / 32);
+			if (blocks > cap) blocks = cap;
+			mul_sliced128_kernel<<<blocks, 96, 0, stream>>>(a, b, o, nb);
+		} else
+			return -1;
+	}
+	return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
+// dependent chain x <- x * y in registers (logic-pipe peak probe)
+__global__ void __launch_bounds__(128) mul_repeat32_kernel(uint32_t* io, uint64_t n_threads, int iters) {
+	const uint64_t g = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+	if (g >= n_threads) return;
+	uint32_t x[32], y[32];
+	load32(io + g * 32, x);
+#pragma unroll
+	for (int i = 0; i < 32; i++) y[i] = x[(i + 1) & 31] ^ 0x9e3779b9u * (i + 1);
+#pragma unroll 1
+	for (int it = 0; it < iters; it++) Sliced<5>::mul(x, y, x);
+	uint4* po = reinterpret_cast<uint4*>(io + g * 32);
+#pragma unroll
+	for (int i = 0; i < 8; i++) po[i] = make_uint4(x[4 * i], x[4 * i + 1], x[4 * i + 2], x[4 * i + 3]);
+}
+
+int launch_mul_repeat(int field_bits, uint32_t* io, uint64_t n_threads, int iters, cudaStream_t stream) {
+	if (field_bits != 32) return -4;
+	if (n_threads == 0) return 0;
+	mul_repeat32_kernel<<<(unsigned)((n_threads + 127) / 128), 128, 0, stream>>>(io, n_threads, iters);
+	return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
+}  // namespace b2

@@ -1,0 +1,245 @@
+// b2ntt.cu -- implementation of the C ABI declared in include/b2ntt.h (libb2ntt.so).
+// Host logic only: plan building (b2_plan.h), device buffers, launches.  No CPU fallback: every
+// compute entry point needs a CUDA device and returns B2NTT_ECUDA without one.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <new>
+
+#include "../../include/b2ntt.h"
+#include "b2_launch.h"
+#include "b2_plan.h"
+
+using namespace b2;
+
+static thread_local char g_cuda_err[256] = "";
+
+static int cuda_fail(cudaError_t e, const char* where) {
+	snprintf(g_cuda_err, sizeof g_cuda_err, "%s: %s", where, cudaGetErrorString(e));
+	cudaGetLastError();
+	return B2NTT_ECUDA;
+}
+#define CU(call)                                              \
+	do {                                                      \
+		cudaError_t e_ = (call);                              \
+		if (e_ != cudaSuccess) return cuda_fail(e_, #call);   \
+	} while (0)
+
+struct b2ntt_plan {
+	HostPlan hp;
+	int device = 0;
+	uint32_t* d_consts = nullptr;   // [32][kConstPitch]
+	uint32_t* d_lane_tw = nullptr;  // [5][32]
+	// exec_host staging
+	cudaStream_t stream = nullptr;
+	uint32_t* d_in = nullptr;
+	uint32_t* d_out = nullptr;
+};
+
+static size_t elem_words(const HostPlan& hp) { return (size_t)1 << hp.limbs_log; }
+static size_t in_words(const HostPlan& hp) { return ((size_t)hp.batch << hp.log_h) * elem_words(hp); }
+static size_t out_words(const HostPlan& hp) { return in_words(hp) << hp.log_rate; }
+
+extern "C" int b2ntt_plan_create(b2ntt_plan** out, int field_bits, int layout, int log_h, int log_rate, int batch, int device) {
+	if (!out) return B2NTT_EINVAL;
+	*out = nullptr;
+	if (!plan_args_ok(field_bits, layout, log_h, log_rate, batch)) return B2NTT_EINVAL;
+	int ndev = 0;
+	if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return cuda_fail(cudaErrorNoDevice, "cudaGetDeviceCount");
+	if (device < 0 || device >= ndev) return B2NTT_EINVAL;
+	b2ntt_plan* p = new (std::nothrow) b2ntt_plan;
+	if (!p) return B2NTT_ENOMEM;
+	if (plan_build(p->hp, field_bits, layout, log_h, log_rate, batch)) {
+		delete p;
+		return B2NTT_EINVAL;
+	}
+	p->device = device;
+	cudaError_t e = cudaSetDevice(device);
+	if (e == cudaSuccess) e = cudaMalloc(&p->d_consts, sizeof p->hp.consts);
+	if (e == cudaSuccess) e = cudaMalloc(&p->d_lane_tw, sizeof p->hp.lane_tw);
+	if (e == cudaSuccess) e = cudaMemcpy(p->d_consts, p->hp.consts, sizeof p->hp.consts, cudaMemcpyHostToDevice);
+	if (e == cudaSuccess) e = cudaMemcpy(p->d_lane_tw, p->hp.lane_tw, sizeof p->hp.lane_tw, cudaMemcpyHostToDevice);
+	if (e != cudaSuccess) {
+		const int rc = e == cudaErrorMemoryAllocation ? B2NTT_ENOMEM : cuda_fail(e, "plan_create");
+		b2ntt_plan_destroy(p);
+		return rc;
+	}
+	*out = p;
+	return B2NTT_OK;
+}
+
+extern "C" int b2ntt_plan_destroy(b2ntt_plan* p) {
+	if (!p) return B2NTT_OK;
+	cudaSetDevice(p->device);
+	if (p->d_consts) cudaFree(p->d_consts);
+	if (p->d_lane_tw) cudaFree(p->d_lane_tw);
+	if (p->d_in) cudaFree(p->d_in);
+	if (p->d_out) cudaFree(p->d_out);
+	if (p->stream) cudaStreamDestroy(p->stream);
+	delete p;
+	return B2NTT_OK;
+}
+
+static void fill_pass(const b2ntt_plan* p, PassParams& P, const PassDesc& pd, const uint32_t* src, uint32_t* dst, bool first_pass,
+                      bool inverse, int coset) {
+	const HostPlan& hp = p->hp;
+	memset(&P, 0, sizeof P);
+	const uint64_t row_words = (uint64_t)32 << hp.nb;
+	const int rows = inverse ? hp.batch : hp.batch << hp.log_rate;
+	P.src = first_pass ? src : dst;
+	P.dst = dst;
+	P.src_row_words = row_words;
+	P.dst_row_words = row_words;
+	P.src_row_shift = (first_pass && !inverse) ? hp.log_rate : 0;
+	P.coset_mask = inverse ? 0u : ((1u << hp.log_rate) - 1);
+	P.consts = p->d_consts;
+	P.lane_tw = p->d_lane_tw;
+	P.log_h = hp.log_h, P.log_rate = hp.log_rate, P.limbs_log = hp.limbs_log;
+	P.n_inline = hp.n_inline, P.lane_shift = hp.lane_shift, P.batch_bits = hp.batch_bits, P.sliced_io = hp.sliced_io;
+	P.nb = hp.nb, P.q0 = pd.q0, P.k = pd.k, P.in_line = pd.in_line;
+	P.inverse = inverse ? 1 : 0;
+	P.coset0 = inverse ? coset : 0;
+	P.n_tiles = (uint64_t)rows << (hp.nb - pd.k);
+	memcpy(P.cls, hp.cls, 32);
+}
+
+static int run(b2ntt_plan* p, const void* d_in, void* d_out, bool inverse, int coset, cudaStream_t st) {
+	const HostPlan& hp = p->hp;
+	if (!d_in || !d_out) return B2NTT_EINVAL;
+	if (d_in == d_out && hp.log_rate != 0 && !inverse) return B2NTT_EINVAL;
+	CU(cudaSetDevice(p->device));
+	const uint32_t* src = (const uint32_t*)d_in;
+	uint32_t* dst = (uint32_t*)d_out;
+	if (hp.tiny) {
+		TinyParams T;
+		memset(&T, 0, sizeof T);
+		T.src = src, T.dst = dst, T.consts = p->d_consts;
+		T.log_h = hp.log_h, T.log_rate = hp.log_rate, T.limbs_log = hp.limbs_log;
+		T.rows = inverse ? hp.batch : hp.batch << hp.log_rate;
+		T.src_row_shift = inverse ? 0 : hp.log_rate;
+		T.coset_mask = inverse ? 0u : ((1u << hp.log_rate) - 1);
+		T.coset0 = inverse ? (uint32_t)coset : 0u;
+		T.inverse = inverse ? 1 : 0;
+		if (launch_tiny_fanout(T, st)) return cuda_fail(cudaGetLastError(), "tiny_fanout");
+		const uint64_t words = (uint64_t)T.rows << (hp.log_h + hp.limbs_log);
+		const int width = 32 << hp.limbs_log;
+		if (hp.layout == B2NTT_LAYOUT_BITSLICED && launch_bitslice(dst, words / width, width, 1, st))
+			return cuda_fail(cudaGetLastError(), "bitslice");
+		if (launch_tiny_layers(T, st)) return cuda_fail(cudaGetLastError(), "tiny_layers");
+		if (hp.layout == B2NTT_LAYOUT_BITSLICED && launch_bitslice(dst, words / width, width, 0, st))
+			return cuda_fail(cudaGetLastError(), "bitslice");
+		return B2NTT_OK;
+	}
+	PassParams P;
+	const int np = (int)hp.passes.size();
+	for (int n = 0; n < np; n++) {
+		const PassDesc& pd = inverse ? hp.passes[np - 1 - n] : hp.passes[n];
+		fill_pass(p, P, pd, src, dst, n == 0, inverse, coset);
+		if (launch_pass(P, st)) return cuda_fail(cudaGetLastError(), "launch_pass");
+	}
+	return B2NTT_OK;
+}
+
+extern "C" int b2ntt_exec(b2ntt_plan* p, const void* d_in, void* d_out, void* stream) {
+	if (!p) return B2NTT_EINVAL;
+	return run(p, d_in, d_out, false, 0, (cudaStream_t)stream);
+}
+
+extern "C" int b2ntt_exec_inverse(b2ntt_plan* p, const void* d_in, void* d_out, int coset, void* stream) {
+	if (!p) return B2NTT_EINVAL;
+	if (coset < 0 || coset >= (1 << p->hp.log_rate)) return B2NTT_EINVAL;
+	return run(p, d_in, d_out, true, coset, (cudaStream_t)stream);
+}
+
+extern "C" int b2ntt_exec_host(b2ntt_plan* p, const void* h_in, size_t n_in, void* h_out) {
+	if (!p || !h_in || !h_out) return B2NTT_EINVAL;
+	const HostPlan& hp = p->hp;
+	if (n_in != ((size_t)1 << hp.log_h)) return B2NTT_EINVAL;  // additive_ntt.cuh:206-208
+	CU(cudaSetDevice(p->device));
+	if (!p->stream) CU(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
+	const size_t ib = in_words(hp) * 4, ob = out_words(hp) * 4;
+	if (!p->d_out) {
+		cudaError_t e = cudaMalloc(&p->d_out, ob);
+		if (e != cudaSuccess) return e == cudaErrorMemoryAllocation ? (cudaGetLastError(), B2NTT_ENOMEM) : cuda_fail(e, "cudaMalloc");
+	}
+	if (hp.log_rate != 0 && !p->d_in) {
+		cudaError_t e = cudaMalloc(&p->d_in, ib);
+		if (e != cudaSuccess) return e == cudaErrorMemoryAllocation ? (cudaGetLastError(), B2NTT_ENOMEM) : cuda_fail(e, "cudaMalloc");
+	}
+	uint32_t* din = hp.log_rate ? p->d_in : p->d_out;
+	CU(cudaMemcpyAsync(din, h_in, ib, cudaMemcpyHostToDevice, p->stream));
+	const int rc = run(p, din, p->d_out, false, 0, p->stream);
+	if (rc) return rc;
+	CU(cudaMemcpyAsync(h_out, p->d_out, ob, cudaMemcpyDeviceToHost, p->stream));
+	CU(cudaStreamSynchronize(p->stream));
+	return B2NTT_OK;
+}
+
+extern "C" int b2ntt_plan_launches(const b2ntt_plan* p) {
+	if (!p) return B2NTT_EINVAL;
+	const HostPlan& hp = p->hp;
+	if (hp.tiny) return hp.log_h + (hp.log_rate ? 1 : 0) + (hp.layout == B2NTT_LAYOUT_BITSLICED ? 2 : 0);
+	return (int)hp.passes.size();
+}
+extern "C" int b2ntt_plan_passes(const b2ntt_plan* p) {
+	if (!p) return B2NTT_EINVAL;
+	return p->hp.tiny ? p->hp.log_h : (int)p->hp.passes.size();
+}
+extern "C" int b2ntt_plan_constants(const b2ntt_plan* p, uint32_t* h_out) {
+	if (!p || !h_out) return B2NTT_EINVAL;
+	memcpy(h_out, p->hp.consts, sizeof p->hp.consts);
+	return B2NTT_OK;
+}
+
+extern "C" int b2ntt_bitslice(void* d_buf, size_t n_blocks, int width_bits, int dir, void* stream) {
+	if (width_bits != 32 && width_bits != 64 && width_bits != 128) return B2NTT_EINVAL;
+	if (dir != 0 && dir != 1) return B2NTT_EINVAL;
+	if (n_blocks == 0) return B2NTT_OK;
+	if (!d_buf) return B2NTT_EINVAL;
+	if (launch_bitslice((uint32_t*)d_buf, n_blocks, width_bits, dir, (cudaStream_t)stream)) return cuda_fail(cudaGetLastError(), "bitslice");
+	return B2NTT_OK;
+}
+
+extern "C" int b2ntt_mul(int field_bits, int layout, const void* a, const void* b, void* o, size_t n, void* stream) {
+	if (layout == B2NTT_LAYOUT_COMPACT) {
+		if (field_bits != 8 && field_bits != 16 && field_bits != 32 && field_bits != 128) return B2NTT_EINVAL;
+	} else if (layout == B2NTT_LAYOUT_BITSLICED) {
+		if ((field_bits != 32 && field_bits != 128) || n % 32) return B2NTT_EINVAL;
+	} else
+		return B2NTT_EINVAL;
+	if (n == 0) return B2NTT_OK;
+	if (!a || !b || !o) return B2NTT_EINVAL;
+	if (launch_mul(field_bits, layout, (const uint32_t*)a, (const uint32_t*)b, (uint32_t*)o, n, (cudaStream_t)stream))
+		return cuda_fail(cudaGetLastError(), "mul");
+	return B2NTT_OK;
+}
+
+extern "C" int b2ntt_mul_repeat(int field_bits, void* d_io, size_t n_threads, int iters, void* stream) {
+	if (field_bits != 32) return field_bits == 128 ? B2NTT_EUNSUPPORTED : B2NTT_EINVAL;
+	if (!d_io || iters < 0) return B2NTT_EINVAL;
+	if (launch_mul_repeat(field_bits, (uint32_t*)d_io, n_threads, iters, (cudaStream_t)stream)) return cuda_fail(cudaGetLastError(), "mul_repeat");
+	return B2NTT_OK;
+}
+
+// utils/common.cu:6-43: >= 1024 threads per block, > 32 KB shared memory, grid >= (2^20, 2^12, 2^15)
+extern "C" int b2ntt_check_gpu_capabilities(int device) {
+	cudaDeviceProp pr;
+	cudaError_t e = cudaGetDeviceProperties(&pr, device);
+	if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceProperties");
+	const bool ok = pr.maxThreadsPerBlock >= 1024 && pr.sharedMemPerBlock > (1u << 15) && pr.maxGridSize[0] >= (1 << 20) &&
+	                pr.maxGridSize[1] >= (1 << 12) && pr.maxGridSize[2] >= (1 << 15) && pr.major >= 10;
+	return ok ? 1 : 0;
+}
+
+extern "C" const char* b2ntt_strerror(int code) {
+	switch (code) {
+		case B2NTT_OK: return "ok";
+		case B2NTT_EINVAL: return "invalid argument";
+		case B2NTT_ENOMEM: return "out of memory";
+		case B2NTT_ECUDA: return "CUDA error or no usable device";
+		case B2NTT_EUNSUPPORTED: return "not supported by this build";
+		default: return "unknown error";
+	}
+}
+extern "C" const char* b2ntt_last_cuda_error(void) { return g_cuda_err; }

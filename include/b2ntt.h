@@ -27,6 +27,9 @@
 #ifdef __cplusplus
 extern "C" {
 #endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)
+#endif
 
 enum {
 	B2NTT_OK = 0,
@@ -98,6 +101,9 @@ const char* b2ntt_strerror(int code);
 /* Text of the last CUDA error seen by the calling thread's last failing call ("" if none). */
 const char* b2ntt_last_cuda_error(void);
 
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
 #ifdef __cplusplus
 }
 #endif

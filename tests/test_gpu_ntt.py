@@ -1,0 +1,144 @@
+"""GPU parity tests of the additive NTT: CUDA path (through the C ABI) vs the CPU oracle on the same
+seeded inputs, vs the reference's golden MD5 table (ntt/tests/test_ntt.cu:52-124), and through
+size-independent properties at full size."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev(x, cuda):
+    import torch
+
+    return torch.from_numpy(x.view(np.int32)).to(cuda)
+
+
+def _host(t):
+    return t.cpu().numpy().view(np.uint32)
+
+
+def _rand(n, seed):
+    return np.random.default_rng(seed).integers(0, 2**32, size=n, dtype=np.uint32)
+
+
+# ---- golden digests: the reference's own test, log_rate 0 and 2 (test_ntt.cu:219-229) ---------------
+@pytest.mark.parametrize("log_rate,log_hs", [(0, range(1, 25)), (2, range(1, 23))])
+def test_golden_md5_gf32(b2, oracle, cuda, log_rate, log_hs):
+    for log_h in log_hs:
+        x = oracle.reference_input(log_h, log_rate)
+        plan = b2.Plan(32, log_h, log_rate)
+        out = plan.exec_host(x)
+        assert oracle.md5_hex(out) == oracle.golden_md5(log_rate, log_h), (log_rate, log_h)
+        plan.close()
+
+
+@pytest.mark.parametrize("log_rate,log_h", [(0, 25), (0, 26), (0, 27), (0, 28), (2, 24), (2, 25), (2, 26)])
+def test_golden_md5_gf32_large(b2, oracle, cuda, log_rate, log_h):
+    x = oracle.reference_input(log_h, log_rate)
+    plan = b2.Plan(32, log_h, log_rate)
+    out = plan.exec_host(x)
+    assert oracle.md5_hex(out) == oracle.golden_md5(log_rate, log_h)
+    plan.close()
+
+
+# ---- oracle parity on random inputs, every log_rate, both fields, device-resident path ------------
+@pytest.mark.parametrize("field_bits", [32, 128])
+@pytest.mark.parametrize("log_rate", [0, 1, 2, 3, 4])
+def test_oracle_parity(b2, oracle, cuda, field_bits, log_rate):
+    limbs = field_bits // 32
+    for log_h in [1, 2, 3, 4, 5, 6, 7, 9, 12, 15, 16, 18]:
+        x = _rand((1 << log_h) * limbs, 1000 * log_h + log_rate)
+        plan = b2.Plan(field_bits, log_h, log_rate)
+        out = _host(plan.exec(_dev(x, cuda)))
+        ref = oracle.antt_forward(x, log_h, log_rate, limbs)
+        assert np.array_equal(out, ref), (field_bits, log_h, log_rate)
+        plan.close()
+
+
+def test_gf128_limb0_is_golden(b2, oracle, cuda):
+    """limb 0 of a GF(2^128) transform fed with the reference stream reproduces the
+    GF(2^32) golden digest."""
+    for log_h, log_rate in [(20, 0), (18, 2), (22, 0)]:
+        x = np.zeros((1 << log_h, 4), dtype=np.uint32)
+        x[:, 0] = oracle.reference_input(log_h, log_rate)
+        x[:, 1:] = _rand((1 << log_h) * 3, 5).reshape(-1, 3)
+        plan = b2.Plan(128, log_h, log_rate)
+        out = plan.exec_host(x.reshape(-1)).reshape(-1, 4)
+        assert oracle.md5_hex(np.ascontiguousarray(out[:, 0])) == oracle.golden_md5(log_rate, log_h)
+        plan.close()
+
+
+@pytest.mark.parametrize("field_bits", [32, 128])
+def test_batch_columns(b2, oracle, cuda, field_bits):
+    limbs = field_bits // 32
+    log_h, log_rate, batch = 11, 2, 5
+    x = _rand(batch * (1 << log_h) * limbs, 77)
+    plan = b2.Plan(field_bits, log_h, log_rate, batch=batch)
+    out = _host(plan.exec(_dev(x, cuda))).reshape(batch, -1)
+    for c in range(batch):
+        ref = oracle.antt_forward(x.reshape(batch, -1)[c], log_h, log_rate, limbs)
+        assert np.array_equal(out[c], ref)
+
+
+@pytest.mark.parametrize("field_bits", [32, 128])
+def test_inverse_roundtrip_and_oracle(b2, oracle, cuda, field_bits):
+    limbs = field_bits // 32
+    for log_h, log_rate in [(3, 0), (10, 0), (14, 2), (20, 1)]:
+        x = _rand((1 << log_h) * limbs, log_h)
+        plan = b2.Plan(field_bits, log_h, log_rate)
+        y = plan.exec(_dev(x, cuda))
+        n = (1 << log_h) * limbs
+        for coset in range(1 << log_rate):
+            back = _host(plan.exec_inverse(y[coset * n:(coset + 1) * n].clone(), coset=coset))
+            assert np.array_equal(back, x), (log_h, log_rate, coset)
+        if log_h <= 14:
+            yi = _host(y)[:n]
+            assert np.array_equal(oracle.antt_inverse(yi, log_h, log_rate, 0, limbs), x)
+
+
+@pytest.mark.parametrize("field_bits", [32, 128])
+def test_bitsliced_layout(b2, oracle, cuda, field_bits):
+    limbs = field_bits // 32
+    for log_h, log_rate in [(5, 0), (6, 1), (8, 0), (13, 2), (17, 0)]:
+        x = _rand((1 << log_h) * limbs, 31 * log_h)
+        xs = oracle.bitslice(x, field_bits)
+        plan = b2.Plan(field_bits, log_h, log_rate, layout=b2.api.LAYOUT_BITSLICED)
+        out = _host(plan.exec(_dev(xs, cuda)))
+        ref = oracle.antt_forward(x, log_h, log_rate, limbs)
+        assert np.array_equal(oracle.unbitslice(out, field_bits), ref), (field_bits, log_h, log_rate)
+
+
+def test_full_size_properties_gf128(b2, oracle, cuda):
+    """log_n = 26 GF(2^128): linearity + limb-0 golden digest + inverse round trip."""
+    import torch
+
+    log_h = 26
+    n = 1 << log_h
+    g = torch.Generator(device=cuda).manual_seed(5)
+    a = torch.randint(-2**31, 2**31 - 1, (n * 4,), dtype=torch.int32, device=cuda, generator=g)
+    b = torch.randint(-2**31, 2**31 - 1, (n * 4,), dtype=torch.int32, device=cuda, generator=g)
+    a.view(-1, 4)[:, 0] = _dev(oracle.reference_input(log_h, 0), cuda)
+    plan = b2.Plan(128, log_h, 0)
+    fa = plan.exec(a.clone())
+    assert oracle.md5_hex(_host(fa.view(-1, 4)[:, 0].contiguous())) == oracle.golden_md5(0, log_h)
+    fb = plan.exec(b.clone())
+    fab = plan.exec(a ^ b)
+    assert torch.equal(fab, fa ^ fb)
+    assert torch.equal(plan.exec_inverse(fa), a)
+
+
+def test_error_paths(b2, cuda):
+    with pytest.raises(b2.B2NTTError):
+        b2.Plan(32, 0, 0)
+    with pytest.raises(b2.B2NTTError):
+        b2.Plan(32, 30, 4)
+    with pytest.raises(b2.B2NTTError):
+        b2.Plan(64, 10, 0)
+    ntt = b2.AdditiveNTT(b2.AdditiveNTTConf(10, 0))
+    bad = b2.NTTData(size=1 << 9)
+    out = b2.NTTData()
+    assert ntt.apply(bad, out) is False
+    good = b2.NTTData(size=1 << 10)
+    good.order = b2.DataOrder.BIT_REVERSED
+    assert ntt.apply(good, out) is False
+    assert b2.check_gpu_capabilities(0)
