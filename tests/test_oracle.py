@@ -1,0 +1,169 @@
+"""CPU tests: the oracle against the reference's golden vectors (pins parity), the oracle against the
+reference's own host field code when oracle/_ref is built, and the CPU emulator of the CUDA pass
+phases against the oracle."""
+import ctypes as C
+import json
+import os
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = json.load(open(os.path.join(ROOT, "tests", "golden", "additive_ntt_md5.json")))["md5"]
+KATS = json.load(open(os.path.join(ROOT, "tests", "golden", "field_kats.json")))
+
+
+def _rand(n, seed):
+    return np.random.default_rng(seed).integers(0, 2**32, size=n, dtype=np.uint32)
+
+
+# ---- NTT: golden MD5 table of ntt/tests/test_ntt.cu:52-124 -----------------------------------------
+@pytest.mark.parametrize("log_rate,max_h", [(0, 22), (2, 20)])
+def test_oracle_reproduces_golden_md5(oracle, log_rate, max_h):
+    for log_h in range(1, max_h + 1):
+        x = oracle.reference_input(log_h, log_rate)
+        y = oracle.antt_forward(x, log_h, log_rate)
+        assert oracle.md5_hex(y) == GOLD[str(log_rate)][str(log_h)], (log_rate, log_h)
+        assert oracle.golden_md5(log_rate, log_h) == GOLD[str(log_rate)][str(log_h)]
+
+
+def test_oracle_plain_and_fast_products_agree(oracle):
+    x = _rand(1 << 10, 3)
+    y = oracle.antt_forward(x, 10, 1)
+    oracle.lib.orc_antt_set_plain(1)
+    try:
+        assert np.array_equal(oracle.antt_forward(x, 10, 1), y)
+    finally:
+        oracle.lib.orc_antt_set_plain(0)
+
+
+def test_gf128_ntt_is_limbwise_and_matches_full_product(oracle):
+    """with subfield twiddles the GF(2^128) transform is four interleaved GF(2^32)
+    transforms; the definitional form multiplies with the full 128-bit tower product."""
+    log_h = 8
+    x = _rand((1 << log_h) * 4, 11)
+    y = oracle.antt_forward(x, log_h, 1, 4)
+    assert np.array_equal(y, oracle.antt_forward_full128(x, log_h, 1))
+    for l in range(4):
+        yl = oracle.antt_forward(np.ascontiguousarray(x.reshape(-1, 4)[:, l]), log_h, 1)
+        assert np.array_equal(y.reshape(-1, 4)[:, l], yl)
+
+
+def test_inverse_inverts(oracle):
+    for limbs in (1, 4):
+        for log_h, log_rate in [(1, 0), (5, 0), (9, 2), (12, 1)]:
+            x = _rand((1 << log_h) * limbs, log_h)
+            y = oracle.antt_forward(x, log_h, log_rate, limbs)
+            n = (1 << log_h) * limbs
+            for c in range(1 << log_rate):
+                assert np.array_equal(oracle.antt_inverse(y[c * n:(c + 1) * n], log_h, log_rate, c, limbs), x)
+
+
+# ---- field: known-answer vectors of finite_fields/tests -----------------------------------------------
+def test_field_kats(oracle):
+    L = oracle.lib
+    for a, b, c in KATS["mul32"]:
+        assert L.orc_mul32(a, b) == c and L.orc_mul32_fast(a, b) == c
+    for a, c in KATS["square32"]:
+        assert L.orc_square32(a) == c
+    for a, c in KATS["inverse32"]:
+        assert L.orc_inverse32(a) == c
+    for h, a, b, c in KATS["packed_mul"]:
+        assert L.orc_mul_packed32(a, b, h) == c, (h, hex(a), hex(b))
+
+
+def test_bitsliced_kats(oracle):
+    for case in KATS["bitsliced"]:
+        h = case["h"]
+        w = 1 << h
+        a = np.zeros(w, dtype=np.uint32)
+        b = np.zeros(w, dtype=np.uint32)
+        a[:len(case["a"])] = case["a"]
+        b[:len(case["b"])] = case["b"]
+        r = oracle.unbitslice(oracle.mul_bitsliced(oracle.bitslice(a, w), oracle.bitslice(b, w), h), w)
+        for i, v in case["result"].items():
+            assert r[int(i)] == v, (h, i)
+        # the compact product agrees with the bit-sliced one (ties compact GF(2^128) to the KATs)
+        if h == 7:
+            assert np.array_equal(oracle.mul128(a, b).reshape(-1), r)
+        else:
+            assert np.array_equal(oracle.mul32(a, b), r)
+
+
+def test_oracle_matches_reference_host_code(oracle):
+    R = oracle.ref_lib()
+    if R is None:
+        pytest.skip("oracle/_ref not built (needs /root/reference)")
+    rng = np.random.default_rng(5)
+    for _ in range(300):
+        a, b = (int(v) for v in rng.integers(0, 2**32, 2))
+        assert R.ref_mul(a, b, 5) == oracle.lib.orc_mul32(a, b)
+        assert R.ref_square(a, 5) == oracle.lib.orc_square32(a)
+        assert R.ref_inverse(a, 5) == oracle.lib.orc_inverse32(a)
+    for h in (5, 7):
+        w = 1 << h
+        a, b = _rand(w, 1), _rand(w, 2)
+        out = np.empty(w, dtype=np.uint32)
+        R.ref_mul_unrolled(a, b, out, h)
+        assert np.array_equal(out, oracle.mul_bitsliced(a, b, h))
+        t = a.copy()
+        R.ref_bitslice(t, w)
+        assert np.array_equal(t, oracle.bitslice(a, w))
+    a, b = _rand(4, 3), _rand(4, 4)
+    out = np.empty(4, dtype=np.uint32)
+    R.ref_mul128_words(a, b, out)
+    assert np.array_equal(out, oracle.mul128(a, b).reshape(-1))
+
+
+# ---- CPU emulation of the CUDA pass phases (same source as the kernels) -------------------------------
+@pytest.fixture(scope="module")
+def emul():
+    p = os.path.join(ROOT, "tests", "emul", "libb2emul.so")
+    if not os.path.exists(p):
+        import subprocess
+
+        subprocess.run(["make", "-C", os.path.dirname(p)], check=True)
+    E = C.CDLL(p)
+    u32p = np.ctypeslib.ndpointer(dtype=np.uint32, flags="C_CONTIGUOUS")
+    E.emul_antt.argtypes = [C.c_int] * 5 + [u32p, u32p, C.c_int, C.c_int]
+    E.emul_constants.argtypes = [C.c_int, C.c_int, u32p]
+    E.emul_gf32_mul.argtypes = [C.c_uint32, C.c_uint32]
+    E.emul_gf32_mul.restype = C.c_uint32
+    E.emul_sliced_mul.argtypes = [u32p, u32p, u32p, C.c_int]
+    return E
+
+
+@pytest.mark.parametrize("field_bits,layout,log_h,log_rate", [
+    (32, 0, 6, 0), (32, 0, 12, 0), (32, 0, 15, 2), (128, 0, 4, 0), (128, 0, 10, 0), (128, 0, 13, 1),
+    (32, 1, 9, 0), (128, 1, 8, 1), (32, 0, 16, 0)])
+def test_emulated_kernels_match_oracle(oracle, emul, field_bits, layout, log_h, log_rate):
+    limbs = field_bits // 32
+    x = _rand((1 << log_h) * limbs, 17 * log_h + log_rate)
+    src = oracle.bitslice(x, field_bits) if layout else x
+    out = np.zeros((1 << (log_h + log_rate)) * limbs, dtype=np.uint32)
+    assert emul.emul_antt(field_bits, layout, log_h, log_rate, 1, src, out, 0, 0) == 0
+    got = oracle.unbitslice(out, field_bits) if layout else out
+    ref = oracle.antt_forward(x, log_h, log_rate, limbs)
+    assert np.array_equal(got, ref)
+    # inverse of coset 0
+    n = (1 << log_h) * limbs
+    back = np.zeros(n, dtype=np.uint32)
+    assert emul.emul_antt(field_bits, layout, log_h, log_rate, 1, np.ascontiguousarray(out[:n]), back, 1, 0) == 0
+    assert np.array_equal(back, src)
+
+
+def test_plan_constants_and_products_match_oracle(oracle, emul):
+    for log_h, log_rate in [(20, 0), (20, 2), (28, 0), (28, 4)]:
+        c = np.zeros(32 * 32, dtype=np.uint32)
+        emul.emul_constants(log_h, log_rate, c)
+        ref = oracle.antt_constants(log_h, log_rate)
+        assert np.array_equal(c.reshape(32, 32)[:log_h, :ref.shape[1]], ref)
+    rng = np.random.default_rng(9)
+    for _ in range(200):
+        a, b = (int(v) for v in rng.integers(0, 2**32, 2))
+        assert emul.emul_gf32_mul(a, b) == oracle.lib.orc_mul32(a, b)
+    for h in (2, 3, 4, 5, 6, 7):
+        a, b = _rand(1 << h, h), _rand(1 << h, h + 50)
+        out = np.empty(1 << h, dtype=np.uint32)
+        emul.emul_sliced_mul(a, b, out, h)
+        assert np.array_equal(out, oracle.mul_bitsliced(a, b, h))
