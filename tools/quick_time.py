@@ -25,9 +25,31 @@ def time_plan(field_bits, log_h, log_rate=0, layout=0, batch=1, iters=5):
                           ms=round(ms, 4), gel_s=round(n_out / ms / 1e6, 3), alg_gbs=round(bytes_alg / ms / 1e6, 1))), flush=True)
     plan.close()
 
-if __name__ == "__main__":
+def main():
     shapes = [(32, 20), (32, 24), (32, 28), (128, 20), (128, 24), (128, 26), (128, 28)]
     for fb, lh in shapes:
         time_plan(fb, lh)
     time_plan(32, 20, 2, batch=16)
     time_plan(128, 24, 0, layout=1)
+    logic_peak()
+
+
+def logic_peak(iters=200, lop3_per_mul=990):
+    """Dependent-chain bit-sliced GF(2^32) products in registers: LOP3 issue rate of the ALU pipe."""
+    nthreads = 148 * 1024
+    io = torch.randint(-2**31, 2**31 - 1, (nthreads * 32,), dtype=torch.int32, device="cuda")
+    b2.mul_repeat(io, 32, 10)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    b2.mul_repeat(io, 32, iters)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    ops = nthreads * iters * lop3_per_mul
+    print(json.dumps(dict(probe="mul_repeat32", ms=round(ms, 3), lop3_per_s=ops / ms * 1e3,
+                          lop3_per_clk_per_sm_at_1965MHz=ops / ms * 1e3 / 148 / 1.965e9)), flush=True)
+
+
+if __name__ == "__main__":
+    main()
