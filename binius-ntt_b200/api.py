@@ -20,7 +20,8 @@ class B2NTTError(RuntimeError):
 
 
 def lib_path():
-    return os.path.join(HERE, "libb2ntt.so")
+    # B2NTT_LIB: development override to compare differently tuned builds of the same library
+    return os.environ.get("B2NTT_LIB") or os.path.join(HERE, "libb2ntt.so")
 
 
 def lib():

@@ -7,42 +7,62 @@
 #include "b2_launch.h"
 #include "b2_pass.cuh"
 
+#ifndef B2_WARPS_PER_SM
+#define B2_WARPS_PER_SM 8  // resident warps per SM the pass kernels are compiled for (register budget 65536 / (32 * this))
+#endif
+
 namespace b2 {
 
-// One CTA = 256 threads = up to 512 lines (64 KiB) of the data set, grouped as 2^(9-k) tiles of
-// 2^k lines.  Every thread keeps two bundles (64 registers) and runs one butterfly per layer;
-// between layers the bundles are exchanged through swizzled shared memory.
-template <bool INV>
-__global__ void __launch_bounds__(kCtaThreads, 1) pass_kernel(const __grid_constant__ PassParams P) {
-	extern __shared__ __align__(16) unsigned char smem_raw[];
-	PassSmem& sm = *reinterpret_cast<PassSmem*>(smem_raw);
+// A CTA of T threads works through groups of 2T lines (grid-stride, persistent): coalesced
+// cp.async copy-in, k butterfly layers with the bundles exchanged through swizzled shared memory,
+// coalesced copy-out.  Several small CTAs per SM (4 x 64, 2 x 128 or 1 x 256 threads at ~250
+// registers per thread) run out of phase, so one CTA's copies overlap another's logic.
+template <bool INV, int T>
+__global__ void __launch_bounds__(T, B2_WARPS_PER_SM * 32 / T) pass_kernel(const __grid_constant__ PassParams P) {
+	extern __shared__ __align__(16) uint32_t smem_raw[];
+	PassSmem sm = pass_smem_view(smem_raw, T);
 	const int tid = threadIdx.x;
-	pass_prologue(P, sm, tid, kCtaThreads);
-	__syncthreads();
-	Bundles st;
+	pass_prologue(P, sm, tid);
 #pragma unroll 1
-	for (int step = 0; step < P.k; step++) {
-		const int i = pass_layer_bit(P, step);
-		pass_layer<INV>(P, sm, blockIdx.x, tid, i, step == 0, step == P.k - 1, st);
+	for (uint64_t grp = blockIdx.x; grp < P.n_groups; grp += gridDim.x) {
+		group_prologue(P, sm, grp, tid);
+		group_copy<false>(P, sm, grp, tid);
+		__syncthreads();
+#pragma unroll 1
+		for (int step = 0; step < P.k; step++) {
+			const int i = pass_layer_bit(P, step);
+			pass_layer<INV>(P, sm, grp, tid, i, step == 0, step == P.k - 1);
+			__syncthreads();
+		}
+		group_copy<true>(P, sm, grp, tid);
 		__syncthreads();
 	}
 }
 
-int launch_pass(const PassParams& P, cudaStream_t stream) {
-	static bool attr_set = false;
-	if (!attr_set) {
-		cudaFuncSetAttribute(pass_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PassSmem));
-		cudaFuncSetAttribute(pass_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PassSmem));
-		attr_set = true;
+template <bool INV, int T>
+static int launch_pass_t(const PassParams& P, cudaStream_t stream) {
+	int sms = 0;
+	const size_t smem = pass_smem_words(T, 1) * sizeof(uint32_t);
+	{
+		int dev = 0;
+		cudaGetDevice(&dev);
+		cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+		cudaFuncSetAttribute(pass_kernel<INV, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 	}
-	const uint64_t tiles_per_cta = kCtaThreads >> (P.k - 1);
-	const uint64_t ctas = (P.n_tiles + tiles_per_cta - 1) / tiles_per_cta;
-	if (ctas == 0 || ctas > 0x7fffffffull) return -1;
-	if (P.inverse)
-		pass_kernel<true><<<(unsigned)ctas, kCtaThreads, sizeof(PassSmem), stream>>>(P);
-	else
-		pass_kernel<false><<<(unsigned)ctas, kCtaThreads, sizeof(PassSmem), stream>>>(P);
+	uint64_t ctas = (uint64_t)sms * (B2_WARPS_PER_SM * 32 / T) * 4;  // a few waves of groups per CTA slot for balance
+	if (ctas > P.n_groups) ctas = P.n_groups;
+	if (ctas == 0) return -1;
+	pass_kernel<INV, T><<<(unsigned)ctas, T, smem, stream>>>(P);
 	return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
+int launch_pass(const PassParams& P, cudaStream_t stream) {
+	switch (P.cta_threads) {
+		case 64: return P.inverse ? launch_pass_t<true, 64>(P, stream) : launch_pass_t<false, 64>(P, stream);
+		case 128: return P.inverse ? launch_pass_t<true, 128>(P, stream) : launch_pass_t<false, 128>(P, stream);
+		case 256: return P.inverse ? launch_pass_t<true, 256>(P, stream) : launch_pass_t<false, 256>(P, stream);
+	}
+	return -1;
 }
 
 // ------------------------------------------------------------------------------------------------

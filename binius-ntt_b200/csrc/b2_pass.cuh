@@ -6,24 +6,33 @@
 //
 //   element index  e  = line * EPL + lane_elem          EPL = 32 / limbs elements per 128-B line
 //   line index     l  = (hi << (q0+k)) | (x << q0) | lo   x = the k line bits this pass owns
-//   a tile             = the 2^k lines of one (coset row, hi, lo); it lives in shared memory,
-//                        bit-sliced, for the whole pass
+//   a tile             = the 2^k lines of one (coset row, hi, lo)
+//   a group            = the 2T lines a CTA of T threads holds in shared memory at a time:
+//                        2T >> k tiles with consecutive tile numbers (neighbouring `lo`)
 //   thread t of a tile = one butterfly per layer: layer i (line bit q0+i) pairs the lines
 //                        x_u = t with a 0 inserted at bit i, x_v = x_u | 1 << i
 //
-// The per-thread work is written as phase functions (prologue / layer / epilogue) that take the
-// thread identity as arguments: the __global__ wrapper in b2_kernels.cu calls them with
-// __syncthreads() between phases, and tests/emul drives the very same functions thread by thread
-// on the CPU, which is how the indexing is checked in a container without a GPU.
+// Lines travel global -> shared memory as coalesced 16-byte chunks (cp.async on the GPU), are
+// held bit-sliced ("bundles") while the layers run, and go back the same way.  Between passes
+// the data set stays bit-sliced in HBM; only the first load and the last store of a transform on
+// compact images transpose.
+//
+// Twiddles are never recomputed per butterfly: a layer's twiddle is linear in the butterfly-block
+// index (additive_ntt.cuh:59-77), so w = tw_hi[tile][layer] ^ tw_lo[layer][t >> i], two tables in
+// shared memory filled once per CTA (tw_lo) and once per group (tw_hi).
+//
+// The per-thread work is written as phase functions that take the thread identity as arguments:
+// the __global__ wrapper in b2_kernels.cu calls them with __syncthreads() between phases, and
+// tests/emul drives the very same functions thread by thread on the CPU, which is how the
+// indexing is checked in a container without a GPU.
 #pragma once
 #include "b2_bundle.cuh"
 
 namespace b2 {
 
-constexpr int kMaxPassBits = 9;        // up to 512 lines (64 KiB) per tile group
-constexpr int kCtaThreads = 256;       // 2^(kMaxPassBits-1)
-constexpr int kLinesPerCta = 512;      // tiles of 2^k lines are grouped to fill this
-constexpr int kConstPitch = 32;        // words per layer in the constants table
+constexpr int kMaxPassBits = 9;      // up to 512 lines (64 KiB) per group
+constexpr int kMaxCtaThreads = 256;  // 2^(kMaxPassBits-1)
+constexpr int kConstPitch = 32;      // words per layer in the constants table
 
 struct PassParams {
 	const uint32_t* src;   // pass input: row r reads words [ (r >> src_row_shift) * src_row_words, ... )
@@ -40,15 +49,18 @@ struct PassParams {
 	int n_inline;    // butterfly layers inside a line: 5 - limbs_log (compact), 5 (bit-sliced images)
 	int lane_shift;  // in-line layer s pairs lanes differing in bit s + lane_shift
 	int batch_bits;  // low line bits that are not butterfly bits (the limb index of a bit-sliced image)
-	int sliced_io;   // 1: lines in memory are already bit-sliced words (no transposes on load / store)
+	int src_sliced;  // 1: lines of the pass input are bit-sliced words (no transpose on load)
+	int dst_sliced;  // 1: lines of the pass output stay bit-sliced (no transpose on store)
 	int nb;          // line bits per row = log_h + limbs_log - 5
 	int q0;          // first line bit of this pass (>= batch_bits)
-	int k;           // line bits fused in this pass (1..kMaxPassBits)
+	int k;           // line bits fused in this pass (1..log2(2T))
 	int in_line;     // 1: also run the layers inside a line (the pass with q0 == batch_bits)
 	int inverse;     // 0: forward, 1: inverse transform (layers in the opposite order)
 	int coset0;      // coset index of row 0 (inverse transform of one coset)
-	uint64_t n_tiles;  // rows << (nb - k)
-	uint8_t cls[32];   // per layer: 0 = twiddle is always 0, else log2 of the twiddle subfield bits (2..5)
+	int cta_threads; // T
+	uint64_t n_tiles;   // rows << (nb - k)
+	uint64_t n_groups;  // ceil(n_tiles / (2T >> k))
+	uint8_t cls[32];    // per layer: 0 = twiddle is always 0, else log2 of the twiddle subfield bits (2..5)
 };
 
 struct Bundles {
@@ -56,14 +68,26 @@ struct Bundles {
 	uint32_t B[32];
 };
 
-// shared-memory image: constants, then bundle slots
+// shared-memory image (32-bit words), sized by T = cta_threads
 struct PassSmem {
-	uint32_t consts[32 * kConstPitch];
-	uint32_t lane_tw[5 * 32];
-	uint32_t pad[96];
-	uint32_t slots[kLinesPerCta * 32];
+	uint32_t* lane_tw;  // [5][32]
+	uint32_t* tw_lo;    // [2T]   heap order: layer i owns [2^(k-1-i), 2^(k-i))
+	uint32_t* tw_hi;    // [T]    [tile_in_group * k + i]
+	uint32_t* slots;    // [2T][32]
+	uint32_t* inl_lo;   // [5][2T] in-line layers, by line x of the tile
+	uint32_t* inl_hi;   // [5][T]  in-line layers, by tile of the group
 };
-static_assert(sizeof(PassSmem) == 4096 + 640 + 384 + 65536, "layout");
+B2_HD size_t pass_smem_words(int T, int in_line) { return 160 + 2 * (size_t)T + T + 64 * (size_t)T + (in_line ? 15 * (size_t)T : 0); }
+B2_HD PassSmem pass_smem_view(uint32_t* base, int T) {
+	PassSmem sm;
+	sm.slots = base;  // first: 16-byte aligned for the vector accesses
+	sm.lane_tw = sm.slots + 64 * (size_t)T;
+	sm.tw_lo = sm.lane_tw + 160;
+	sm.tw_hi = sm.tw_lo + 2 * T;
+	sm.inl_lo = sm.tw_hi + T;
+	sm.inl_hi = sm.inl_lo + 10 * T;
+	return sm;
+}
 
 // 16-byte groups of a slot are XOR-swizzled by the slot number so that a quarter warp that reads
 // group g of eight different slots touches eight different bank groups.
@@ -72,27 +96,58 @@ B2_HD int slot_word(int slot, int word) {
 	return slot * 32 + (g << 2) + (word & 3);
 }
 
-B2_HD void pass_prologue(const PassParams& P, PassSmem& sm, int tid, int nthreads) {
-	for (int i = tid; i < 32 * kConstPitch; i += nthreads) sm.consts[i] = P.consts[i];
-	for (int i = tid; i < 5 * 32; i += nthreads) sm.lane_tw[i] = P.lane_tw[i];
+// XOR of table[b] over the set bits b of `bits`, table in global or shared memory
+B2_HD uint32_t xor_select64(const uint32_t* table, uint64_t bits) {
+	uint32_t w = 0;
+#pragma unroll 1
+	for (int b = 0; bits; b++, bits >>= 1)
+		if (bits & 1u) w ^= table[b];
+	return w;
+}
+
+B2_HD int pass_stage(const PassParams& P, int i) { return P.n_inline + P.q0 - P.batch_bits + i; }
+
+// once per CTA: tile-independent twiddle tables
+B2_HD void pass_prologue(const PassParams& P, PassSmem& sm, int tid) {
+	const int T = P.cta_threads;
+	for (int i = tid; i < 5 * 32; i += T) sm.lane_tw[i] = P.lane_tw[i];
+	for (int idx = tid; idx < (1 << P.k); idx += T) {
+		if (idx == 0) {
+			sm.tw_lo[0] = 0;
+			continue;
+		}
+		int lg = 31;
+		while (!((uint32_t)idx >> lg)) lg--;
+		const int i = P.k - 1 - lg;  // layer
+		const uint32_t j = (uint32_t)idx - (1u << lg);
+		sm.tw_lo[idx] = xor_select64(P.consts + pass_stage(P, i) * kConstPitch, j);
+	}
+	if (P.in_line) {
+		const int L0 = P.n_inline;
+		for (int idx = tid; idx < L0 << P.k; idx += T) {
+			const int s = idx >> P.k, x = idx & ((1 << P.k) - 1);
+			sm.inl_lo[s * 2 * T + x] = xor_select64(P.consts + s * kConstPitch, (uint64_t)x << (L0 - 1 - s));
+		}
+	}
 }
 
 struct TileCoord {
 	bool active;
-	int slot_base;     // first slot of this thread's tile inside the CTA
+	int tile_in_group;
+	int slot_base;     // first slot of this tile inside the group
 	int t;             // thread index inside the tile
 	uint32_t row;      // coset row
 	uint64_t hi, lo;   // line index parts
 };
 
-B2_HD TileCoord tile_coord(const PassParams& P, uint32_t cta, int tid) {
+B2_HD TileCoord tile_coord_of(const PassParams& P, uint64_t group, int tile_in_group) {
 	TileCoord c;
-	const int tpt = 1 << (P.k - 1);  // threads per tile
-	const int tile_in_cta = tid / tpt;
-	c.t = tid % tpt;
-	const uint64_t tile = (uint64_t)cta * (kCtaThreads / tpt) + tile_in_cta;
+	const int tpg = (2 * P.cta_threads) >> P.k;  // tiles per group
+	const uint64_t tile = group * tpg + tile_in_group;
+	c.tile_in_group = tile_in_group;
+	c.t = 0;
 	c.active = tile < P.n_tiles;
-	c.slot_base = tile_in_cta << P.k;
+	c.slot_base = tile_in_group << P.k;
 	const int tb = P.nb - P.k;  // tile bits per row
 	c.row = (uint32_t)(tile >> tb);
 	const uint64_t tau = tile & ((uint64_t(1) << tb) - 1);
@@ -100,31 +155,81 @@ B2_HD TileCoord tile_coord(const PassParams& P, uint32_t cta, int tid) {
 	c.hi = tau >> P.q0;
 	return c;
 }
+B2_HD TileCoord tile_coord(const PassParams& P, uint64_t group, int tid) {
+	const int tpt = 1 << (P.k - 1);  // threads per tile
+	TileCoord c = tile_coord_of(P, group, tid / tpt);
+	c.t = tid % tpt;
+	return c;
+}
 
 B2_HD uint64_t line_of(const PassParams& P, const TileCoord& c, int x) {
 	return (c.hi << (P.q0 + P.k)) | ((uint64_t)x << P.q0) | c.lo;
 }
 
-B2_HD void load_line(const uint32_t* p, uint32_t* w) {
-#if defined(__CUDA_ARCH__)
-	const uint4* q = reinterpret_cast<const uint4*>(p);
-#pragma unroll
-	for (int g = 0; g < 8; g++) {
-		uint4 v = q[g];
-		w[4 * g] = v.x, w[4 * g + 1] = v.y, w[4 * g + 2] = v.z, w[4 * g + 3] = v.w;
+// once per group: the tile-dependent part of every layer's twiddle
+B2_HD void group_prologue(const PassParams& P, PassSmem& sm, uint64_t group, int tid) {
+	const int T = P.cta_threads;
+	const int tpg = (2 * T) >> P.k;
+	for (int idx = tid; idx < tpg * P.k; idx += T) {
+		const int tig = idx / P.k, i = idx % P.k;
+		const TileCoord c = tile_coord_of(P, group, tig);
+		const int stage = pass_stage(P, i);
+		const uint64_t ind = ((uint64_t)(P.coset0 + (c.row & P.coset_mask)) << (P.log_h - 1 - stage)) | (c.hi << (P.k - 1 - i));
+		sm.tw_hi[idx] = c.active ? xor_select64(P.consts + stage * kConstPitch, ind) : 0u;
 	}
+	if (P.in_line) {
+		const int L0 = P.n_inline;
+		for (int idx = tid; idx < tpg * L0; idx += T) {
+			const int tig = idx / L0, s = idx % L0;
+			const TileCoord c = tile_coord_of(P, group, tig);
+			const uint64_t ind = ((uint64_t)(P.coset0 + (c.row & P.coset_mask)) << (P.log_h - 1 - s)) | (c.hi << (P.k + L0 - 1 - s));
+			sm.inl_hi[s * T + tig] = c.active ? xor_select64(P.consts + s * kConstPitch, ind) : 0u;
+		}
+	}
+}
+
+// ---- global <-> shared memory, 16-byte chunks, coalesced over the group's lines -----------------
+B2_HD void copy16_g2s(uint32_t* s, const uint32_t* g) {
+#if defined(__CUDA_ARCH__)
+	const unsigned sa = (unsigned)__cvta_generic_to_shared(s);
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(g) : "memory");
 #else
-	for (int i = 0; i < 32; i++) w[i] = p[i];
+	for (int j = 0; j < 4; j++) s[j] = g[j];
 #endif
 }
-B2_HD void store_line(uint32_t* p, const uint32_t* w) {
+B2_HD void copy_wait_all() {
 #if defined(__CUDA_ARCH__)
-	uint4* q = reinterpret_cast<uint4*>(p);
-#pragma unroll
-	for (int g = 0; g < 8; g++) q[g] = make_uint4(w[4 * g], w[4 * g + 1], w[4 * g + 2], w[4 * g + 3]);
-#else
-	for (int i = 0; i < 32; i++) p[i] = w[i];
+	asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
 #endif
+}
+B2_HD void copy16_s2g(uint32_t* g, const uint32_t* s) {
+#if defined(__CUDA_ARCH__)
+	*reinterpret_cast<uint4*>(g) = *reinterpret_cast<const uint4*>(s);
+#else
+	for (int j = 0; j < 4; j++) g[j] = s[j];
+#endif
+}
+
+// chunk c of a group: piece = c & 7 (16 bytes of a line), then the tile (neighbouring lines in
+// memory), then the line x of the tile
+template <bool STORE>
+B2_HD void group_copy(const PassParams& P, PassSmem& sm, uint64_t group, int tid) {
+	const int T = P.cta_threads;
+	const int tpg = (2 * T) >> P.k;
+#pragma unroll 4
+	for (int c = tid; c < 16 * T; c += T) {
+		const int piece = c & 7, r = c >> 3;
+		const int tig = r % tpg, x = r / tpg;
+		const TileCoord tc = tile_coord_of(P, group, tig);
+		if (!tc.active) continue;
+		uint32_t* s = &sm.slots[slot_word(tc.slot_base + x, piece * 4)];
+		const uint64_t off = line_of(P, tc, x) * 32 + piece * 4;
+		if (STORE)
+			copy16_s2g(P.dst + (uint64_t)tc.row * P.dst_row_words + off, s);
+		else
+			copy16_g2s(s, P.src + (uint64_t)(tc.row >> P.src_row_shift) * P.src_row_words + off);
+	}
+	if (!STORE) copy_wait_all();
 }
 
 B2_HD void slot_load(const PassSmem& sm, int slot, uint32_t* w) {
@@ -173,69 +278,53 @@ B2_HD void in_line_dispatch(int cls, uint32_t* A, uint32_t* B, int p, const uint
 	}
 }
 
-// twiddle of layer `stage` for the butterfly block `block` of coset row `row`
-B2_HD uint32_t layer_twiddle(const PassParams& P, const PassSmem& sm, int stage, uint32_t row, uint64_t block) {
-	const uint64_t ind = ((uint64_t)(P.coset0 + (row & P.coset_mask)) << (P.log_h - 1 - stage)) | block;
-	return xor_select(&sm.consts[stage * kConstPitch], (uint32_t)ind);
-}
-
-// The layers inside a line for the two lines held by a thread (global line indices la, lb).
+// The layers inside a line for the two lines (xu, xv of tile tig) held by a thread.
+// block index of lane pair y of line l at layer s: (l << (L0-1-s)) | (y >> (p+1)); the line part
+// is uniform over the line (inl_hi ^ inl_lo), the lane part comes from lane_tw.
 template <bool INV>
-B2_HD void in_line_layers(const PassParams& P, const PassSmem& sm, Bundles& st, uint32_t row, uint64_t la, uint64_t lb) {
-	const int L0 = P.n_inline;
-	la >>= P.batch_bits;
-	lb >>= P.batch_bits;
+B2_HD void in_line_layers(const PassParams& P, const PassSmem& sm, Bundles& st, int tig, int xu, int xv) {
+	const int L0 = P.n_inline, T = P.cta_threads;
 #pragma unroll 1
 	for (int n = 0; n < L0; n++) {
 		const int s = INV ? n : L0 - 1 - n;
 		const int p = s + P.lane_shift;
-		// block index of lane pair x of line l at layer s: (l << (L0-1-s)) | (x >> (p+1));
-		// the line part is uniform over the line, the lane part comes from lane_tw.
-		const uint32_t wa = layer_twiddle(P, sm, s, row, la << (L0 - 1 - s));
-		const uint32_t wb = layer_twiddle(P, sm, s, row, lb << (L0 - 1 - s));
+		const uint32_t wh = sm.inl_hi[s * T + tig];
+		const uint32_t wa = wh ^ sm.inl_lo[s * 2 * T + xu];
+		const uint32_t wb = wh ^ sm.inl_lo[s * 2 * T + xv];
 		in_line_dispatch<INV>(P.cls[s], st.A, st.B, p, &sm.lane_tw[s * 32], wa, wb);
 	}
 }
 
 // One line-stride layer (local bit i) for one thread.
-//   first: operands come from global memory (compact) instead of shared memory
-//   last : results stay in registers (st) for the epilogue instead of going to shared memory
+//   first: the bundles were just copied in (transpose compact lines; inverse: in-line layers first)
+//   last : forward: in-line layers last; transpose back for a compact output
 template <bool INV>
-B2_HD void pass_layer(const PassParams& P, PassSmem& sm, uint32_t cta, int tid, int i, bool first, bool last, Bundles& st) {
-	const TileCoord c = tile_coord(P, cta, tid);
+B2_HD void pass_layer(const PassParams& P, PassSmem& sm, uint64_t group, int tid, int i, bool first, bool last) {
+	const TileCoord c = tile_coord(P, group, tid);
 	if (!c.active) return;
 	const int xu = ((c.t >> i) << (i + 1)) | (c.t & ((1 << i) - 1));
 	const int xv = xu | (1 << i);
+	Bundles st;
+	slot_load(sm, c.slot_base + xu, st.A);
+	slot_load(sm, c.slot_base + xv, st.B);
 	if (first) {
-		const uint32_t* src = P.src + (uint64_t)(c.row >> P.src_row_shift) * P.src_row_words;
-		load_line(src + line_of(P, c, xu) * 32, st.A);
-		load_line(src + line_of(P, c, xv) * 32, st.B);
-		if (!P.sliced_io) {
+		if (!P.src_sliced) {
 			transpose32(st.A);
 			transpose32(st.B);
 		}
-		if (INV && P.in_line) in_line_layers<true>(P, sm, st, c.row, line_of(P, c, xu), line_of(P, c, xv));
-	} else {
-		slot_load(sm, c.slot_base + xu, st.A);
-		slot_load(sm, c.slot_base + xv, st.B);
+		if (INV && P.in_line) in_line_layers<true>(P, sm, st, c.tile_in_group, xu, xv);
 	}
-	const int stage = P.n_inline + P.q0 - P.batch_bits + i;
-	const uint64_t block = (c.hi << (P.k - 1 - i)) | (uint64_t)(c.t >> i);
-	const uint32_t w = layer_twiddle(P, sm, stage, c.row, block);
-	uniform_dispatch<INV>(P.cls[stage], st.A, st.B, w);
-	if (!last) {
-		slot_store(sm, c.slot_base + xu, st.A);
-		slot_store(sm, c.slot_base + xv, st.B);
-	} else {
-		uint32_t* dst = P.dst + (uint64_t)c.row * P.dst_row_words;
-		if (!INV && P.in_line) in_line_layers<false>(P, sm, st, c.row, line_of(P, c, xu), line_of(P, c, xv));
-		if (!P.sliced_io) {
+	const uint32_t w = sm.tw_hi[c.tile_in_group * P.k + i] ^ sm.tw_lo[(1 << (P.k - 1 - i)) + (c.t >> i)];
+	uniform_dispatch<INV>(P.cls[pass_stage(P, i)], st.A, st.B, w);
+	if (last) {
+		if (!INV && P.in_line) in_line_layers<false>(P, sm, st, c.tile_in_group, xu, xv);
+		if (!P.dst_sliced) {
 			transpose32(st.A);
 			transpose32(st.B);
 		}
-		store_line(dst + line_of(P, c, xu) * 32, st.A);
-		store_line(dst + line_of(P, c, xv) * 32, st.B);
 	}
+	slot_store(sm, c.slot_base + xu, st.A);
+	slot_store(sm, c.slot_base + xv, st.B);
 }
 
 // layer order of a pass: forward runs local bits k-1 .. 0, inverse 0 .. k-1

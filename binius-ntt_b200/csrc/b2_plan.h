@@ -27,6 +27,7 @@ struct HostPlan {
 	int n_inline = 0, lane_shift = 0, batch_bits = 0, sliced_io = 0;
 	int nb = 0;          // line bits per row
 	bool tiny = false;   // fewer than two lines of butterfly work per row: element-wise kernels
+	int cta_threads = 128;  // T: a CTA holds 2T lines; at most log2(2T) line layers per pass
 	uint32_t consts[32 * kConstPitch];
 	uint32_t lane_tw[5 * 32];
 	uint8_t cls[32];
@@ -72,7 +73,7 @@ inline int twiddle_class(uint32_t or_of_values) {
 	return 5;
 }
 
-inline int plan_build(HostPlan& hp, int field_bits, int layout, int log_h, int log_rate, int batch) {
+inline int plan_build(HostPlan& hp, int field_bits, int layout, int log_h, int log_rate, int batch, int cta_threads = 0) {
 	if (!plan_args_ok(field_bits, layout, log_h, log_rate, batch)) return -1;
 	hp.field_bits = field_bits, hp.layout = layout, hp.log_h = log_h, hp.log_rate = log_rate, hp.batch = batch;
 	hp.limbs_log = field_bits == 128 ? 2 : 0;
@@ -82,6 +83,10 @@ inline int plan_build(HostPlan& hp, int field_bits, int layout, int log_h, int l
 		hp.n_inline = 5, hp.lane_shift = 0, hp.batch_bits = hp.limbs_log, hp.sliced_io = 1;
 	}
 	hp.nb = log_h + hp.limbs_log - 5;
+	if (cta_threads != 64 && cta_threads != 128 && cta_threads != 256) cta_threads = 128;
+	hp.cta_threads = cta_threads;
+	int max_bits = 0;
+	while ((1 << max_bits) < 2 * cta_threads) max_bits++;
 	plan_constants(log_h, log_rate, hp.consts);
 	for (int s = 0; s < 32; s++) {
 		uint32_t m = 0;
@@ -101,7 +106,7 @@ inline int plan_build(HostPlan& hp, int field_bits, int layout, int log_h, int l
 	hp.passes.clear();
 	hp.tiny = nbf < 1;
 	if (!hp.tiny) {
-		const int np = (nbf + kMaxPassBits - 1) / kMaxPassBits;
+		const int np = (nbf + max_bits - 1) / max_bits;
 		// the lowest pass also runs the in-line layers, so it gets the smallest share of line bits
 		int left = nbf;
 		std::vector<int> ks(np);
@@ -118,6 +123,39 @@ inline int plan_build(HostPlan& hp, int field_bits, int layout, int log_h, int l
 		}
 	}
 	return 0;
+}
+
+// Parameters of the n-th pass in EXECUTION order (forward: highest line bits first; inverse: the
+// reverse).  consts / lane_tw point to wherever the kernels will read the tables (device memory on
+// the GPU, hp's own arrays in the CPU emulation).  Intermediate passes leave the lines bit-sliced.
+inline void plan_fill_pass(const HostPlan& hp, PassParams& P, int n, const uint32_t* src, uint32_t* dst, const uint32_t* consts,
+                           const uint32_t* lane_tw, bool inverse, int coset) {
+	const int np = (int)hp.passes.size();
+	const PassDesc& pd = inverse ? hp.passes[np - 1 - n] : hp.passes[n];
+	memset(&P, 0, sizeof P);
+	const uint64_t row_words = (uint64_t)32 << hp.nb;
+	const int rows = inverse ? hp.batch : hp.batch << hp.log_rate;
+	const bool first_pass = n == 0, last_pass = n == np - 1;
+	P.src = first_pass ? src : dst;
+	P.dst = dst;
+	P.src_row_words = row_words;
+	P.dst_row_words = row_words;
+	P.src_row_shift = (first_pass && !inverse) ? hp.log_rate : 0;
+	P.coset_mask = inverse ? 0u : ((1u << hp.log_rate) - 1);
+	P.consts = consts;
+	P.lane_tw = lane_tw;
+	P.log_h = hp.log_h, P.log_rate = hp.log_rate, P.limbs_log = hp.limbs_log;
+	P.n_inline = hp.n_inline, P.lane_shift = hp.lane_shift, P.batch_bits = hp.batch_bits;
+	P.src_sliced = (hp.sliced_io || !first_pass) ? 1 : 0;
+	P.dst_sliced = (hp.sliced_io || !last_pass) ? 1 : 0;
+	P.nb = hp.nb, P.q0 = pd.q0, P.k = pd.k, P.in_line = pd.in_line;
+	P.inverse = inverse ? 1 : 0;
+	P.coset0 = inverse ? coset : 0;
+	P.cta_threads = hp.cta_threads;
+	P.n_tiles = (uint64_t)rows << (hp.nb - pd.k);
+	const uint64_t tpg = (uint64_t)(2 * hp.cta_threads) >> pd.k;
+	P.n_groups = (P.n_tiles + tpg - 1) / tpg;
+	memcpy(P.cls, hp.cls, 32);
 }
 
 }  // namespace b2

@@ -3,6 +3,7 @@
 // compute entry point needs a CUDA device and returns B2NTT_ECUDA without one.
 #include <cuda_runtime.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <new>
@@ -50,7 +51,9 @@ extern "C" int b2ntt_plan_create(b2ntt_plan** out, int field_bits, int layout, i
 	if (device < 0 || device >= ndev) return B2NTT_EINVAL;
 	b2ntt_plan* p = new (std::nothrow) b2ntt_plan;
 	if (!p) return B2NTT_ENOMEM;
-	if (plan_build(p->hp, field_bits, layout, log_h, log_rate, batch)) {
+	int cta = 0;
+	if (const char* e = getenv("B2NTT_CTA_THREADS")) cta = atoi(e);  // tuning knob: 64, 128 or 256
+	if (plan_build(p->hp, field_bits, layout, log_h, log_rate, batch, cta)) {
 		delete p;
 		return B2NTT_EINVAL;
 	}
@@ -79,29 +82,6 @@ extern "C" int b2ntt_plan_destroy(b2ntt_plan* p) {
 	if (p->stream) cudaStreamDestroy(p->stream);
 	delete p;
 	return B2NTT_OK;
-}
-
-static void fill_pass(const b2ntt_plan* p, PassParams& P, const PassDesc& pd, const uint32_t* src, uint32_t* dst, bool first_pass,
-                      bool inverse, int coset) {
-	const HostPlan& hp = p->hp;
-	memset(&P, 0, sizeof P);
-	const uint64_t row_words = (uint64_t)32 << hp.nb;
-	const int rows = inverse ? hp.batch : hp.batch << hp.log_rate;
-	P.src = first_pass ? src : dst;
-	P.dst = dst;
-	P.src_row_words = row_words;
-	P.dst_row_words = row_words;
-	P.src_row_shift = (first_pass && !inverse) ? hp.log_rate : 0;
-	P.coset_mask = inverse ? 0u : ((1u << hp.log_rate) - 1);
-	P.consts = p->d_consts;
-	P.lane_tw = p->d_lane_tw;
-	P.log_h = hp.log_h, P.log_rate = hp.log_rate, P.limbs_log = hp.limbs_log;
-	P.n_inline = hp.n_inline, P.lane_shift = hp.lane_shift, P.batch_bits = hp.batch_bits, P.sliced_io = hp.sliced_io;
-	P.nb = hp.nb, P.q0 = pd.q0, P.k = pd.k, P.in_line = pd.in_line;
-	P.inverse = inverse ? 1 : 0;
-	P.coset0 = inverse ? coset : 0;
-	P.n_tiles = (uint64_t)rows << (hp.nb - pd.k);
-	memcpy(P.cls, hp.cls, 32);
 }
 
 static int run(b2ntt_plan* p, const void* d_in, void* d_out, bool inverse, int coset, cudaStream_t st) {
@@ -134,8 +114,7 @@ static int run(b2ntt_plan* p, const void* d_in, void* d_out, bool inverse, int c
 	PassParams P;
 	const int np = (int)hp.passes.size();
 	for (int n = 0; n < np; n++) {
-		const PassDesc& pd = inverse ? hp.passes[np - 1 - n] : hp.passes[n];
-		fill_pass(p, P, pd, src, dst, n == 0, inverse, coset);
+		plan_fill_pass(hp, P, n, src, dst, p->d_consts, p->d_lane_tw, inverse, coset);
 		if (launch_pass(P, st)) return cuda_fail(cudaGetLastError(), "launch_pass");
 	}
 	return B2NTT_OK;

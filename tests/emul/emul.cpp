@@ -12,58 +12,39 @@
 
 using namespace b2;
 
-static void fill_params(const HostPlan& hp, PassParams& P, const PassDesc& pd, const uint32_t* src, uint32_t* dst,
-                        bool first_pass, bool inverse, int coset) {
-	memset(&P, 0, sizeof P);
-	const uint64_t row_words = (uint64_t)32 << hp.nb;
-	const int rows = inverse ? hp.batch : hp.batch << hp.log_rate;
-	P.src = first_pass ? src : dst;
-	P.dst = dst;
-	P.src_row_words = row_words;
-	P.dst_row_words = row_words;
-	P.src_row_shift = (first_pass && !inverse) ? hp.log_rate : 0;
-	P.coset_mask = inverse ? 0u : ((1u << hp.log_rate) - 1);
-	P.consts = hp.consts;
-	P.lane_tw = hp.lane_tw;
-	P.log_h = hp.log_h, P.log_rate = hp.log_rate, P.limbs_log = hp.limbs_log;
-	P.n_inline = hp.n_inline, P.lane_shift = hp.lane_shift, P.batch_bits = hp.batch_bits, P.sliced_io = hp.sliced_io;
-	P.nb = hp.nb, P.q0 = pd.q0, P.k = pd.k, P.in_line = pd.in_line;
-	P.inverse = inverse ? 1 : 0;
-	P.coset0 = inverse ? coset : 0;
-	P.n_tiles = (uint64_t)rows << (hp.nb - pd.k);
-	memcpy(P.cls, hp.cls, 32);
-}
-
 template <bool INV>
 static void run_pass(const PassParams& P) {
-	const uint64_t tiles_per_cta = kCtaThreads >> (P.k - 1);
-	const uint64_t ctas = (P.n_tiles + tiles_per_cta - 1) / tiles_per_cta;
-	PassSmem* sm = new PassSmem;
-	std::vector<Bundles> st(kCtaThreads);
-	for (uint64_t cta = 0; cta < ctas; cta++) {
-		for (int t = 0; t < kCtaThreads; t++) pass_prologue(P, *sm, t, kCtaThreads);
+	const int T = P.cta_threads;
+	std::vector<uint32_t> mem(pass_smem_words(T, 1));
+	PassSmem sm = pass_smem_view(mem.data(), T);
+	for (int t = 0; t < T; t++) pass_prologue(P, sm, t);
+	for (uint64_t grp = 0; grp < P.n_groups; grp++) {
+		for (int t = 0; t < T; t++) group_prologue(P, sm, grp, t);
+		for (int t = 0; t < T; t++) group_copy<false>(P, sm, grp, t);
 		for (int step = 0; step < P.k; step++) {
 			const int i = pass_layer_bit(P, step);
-			for (int t = 0; t < kCtaThreads; t++)
-				pass_layer<INV>(P, *sm, (uint32_t)cta, t, i, step == 0, step == P.k - 1, st[t]);
+			for (int t = 0; t < T; t++) pass_layer<INV>(P, sm, grp, t, i, step == 0, step == P.k - 1);
 		}
+		for (int t = 0; t < T; t++) group_copy<true>(P, sm, grp, t);
 	}
-	delete sm;
 }
 
-extern "C" int emul_antt(int field_bits, int layout, int log_h, int log_rate, int batch, const uint32_t* in,
-                         uint32_t* out, int inverse, int coset) {
+extern "C" int emul_antt_cta(int field_bits, int layout, int log_h, int log_rate, int batch, const uint32_t* in,
+                             uint32_t* out, int inverse, int coset, int cta_threads) {
 	HostPlan hp;
-	if (plan_build(hp, field_bits, layout, log_h, log_rate, batch)) return -1;
+	if (plan_build(hp, field_bits, layout, log_h, log_rate, batch, cta_threads)) return -1;
 	if (hp.tiny) return -4;
 	PassParams P;
 	const int np = (int)hp.passes.size();
 	for (int n = 0; n < np; n++) {
-		const PassDesc& pd = inverse ? hp.passes[np - 1 - n] : hp.passes[n];
-		fill_params(hp, P, pd, in, out, n == 0, inverse != 0, coset);
+		plan_fill_pass(hp, P, n, in, out, hp.consts, hp.lane_tw, inverse != 0, coset);
 		if (inverse) run_pass<true>(P); else run_pass<false>(P);
 	}
 	return 0;
+}
+extern "C" int emul_antt(int field_bits, int layout, int log_h, int log_rate, int batch, const uint32_t* in,
+                         uint32_t* out, int inverse, int coset) {
+	return emul_antt_cta(field_bits, layout, log_h, log_rate, batch, in, out, inverse, coset, 0);
 }
 
 extern "C" int emul_plan_passes(int field_bits, int layout, int log_h, int log_rate, int* q0, int* k, int* in_line,
