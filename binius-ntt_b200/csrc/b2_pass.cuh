@@ -33,6 +33,7 @@ namespace b2 {
 constexpr int kMaxPassBits = 9;      // up to 512 lines (64 KiB) per group
 constexpr int kMaxCtaThreads = 256;  // 2^(kMaxPassBits-1)
 constexpr int kConstPitch = 32;      // words per layer in the constants table
+constexpr int kSlotWords = 36;       // padded words per 32-word line slot in shared memory
 
 struct PassParams {
 	const uint32_t* src;   // pass input: row r reads words [ (r >> src_row_shift) * src_row_words, ... )
@@ -58,6 +59,7 @@ struct PassParams {
 	int inverse;     // 0: forward, 1: inverse transform (layers in the opposite order)
 	int coset0;      // coset index of row 0 (inverse transform of one coset)
 	int cta_threads; // T
+	int log_tpg;     // log2 of tiles per group = log2(2T) - k
 	uint64_t n_tiles;   // rows << (nb - k)
 	uint64_t n_groups;  // ceil(n_tiles / (2T >> k))
 	uint8_t cls[32];    // per layer: 0 = twiddle is always 0, else log2 of the twiddle subfield bits (2..5)
@@ -77,11 +79,11 @@ struct PassSmem {
 	uint32_t* inl_lo;   // [5][2T] in-line layers, by line x of the tile
 	uint32_t* inl_hi;   // [5][T]  in-line layers, by tile of the group
 };
-B2_HD size_t pass_smem_words(int T, int in_line) { return 160 + 2 * (size_t)T + T + 64 * (size_t)T + (in_line ? 15 * (size_t)T : 0); }
+B2_HD size_t pass_smem_words(int T, int in_line) { return 160 + 2 * (size_t)T + T + 2 * kSlotWords * (size_t)T + (in_line ? 15 * (size_t)T : 0); }
 B2_HD PassSmem pass_smem_view(uint32_t* base, int T) {
 	PassSmem sm;
 	sm.slots = base;  // first: 16-byte aligned for the vector accesses
-	sm.lane_tw = sm.slots + 64 * (size_t)T;
+	sm.lane_tw = sm.slots + 2 * kSlotWords * (size_t)T;
 	sm.tw_lo = sm.lane_tw + 160;
 	sm.tw_hi = sm.tw_lo + 2 * T;
 	sm.inl_lo = sm.tw_hi + T;
@@ -89,12 +91,10 @@ B2_HD PassSmem pass_smem_view(uint32_t* base, int T) {
 	return sm;
 }
 
-// 16-byte groups of a slot are XOR-swizzled by the slot number so that a quarter warp that reads
-// group g of eight different slots touches eight different bank groups.
-B2_HD int slot_word(int slot, int word) {
-	int g = (word >> 2) ^ ((slot ^ (slot >> 3) ^ (slot >> 6)) & 7);
-	return slot * 32 + (g << 2) + (word & 3);
-}
+// Slots are padded to 36 words: a quarter warp reading the same 16-byte group of eight
+// consecutive slots then touches eight different bank groups, and every access of a thread to its
+// slot is a fixed offset from one base address (no per-access index arithmetic).
+B2_HD int slot_word(int slot, int word) { return slot * kSlotWords + word; }
 
 // XOR of table[b] over the set bits b of `bits`, table in global or shared memory
 B2_HD uint32_t xor_select64(const uint32_t* table, uint64_t bits) {
@@ -142,8 +142,7 @@ struct TileCoord {
 
 B2_HD TileCoord tile_coord_of(const PassParams& P, uint64_t group, int tile_in_group) {
 	TileCoord c;
-	const int tpg = (2 * P.cta_threads) >> P.k;  // tiles per group
-	const uint64_t tile = group * tpg + tile_in_group;
+	const uint64_t tile = group * (uint64_t)((2 * P.cta_threads) >> P.k) + tile_in_group;  // tiles per group = 2T >> k
 	c.tile_in_group = tile_in_group;
 	c.t = 0;
 	c.active = tile < P.n_tiles;
@@ -156,9 +155,8 @@ B2_HD TileCoord tile_coord_of(const PassParams& P, uint64_t group, int tile_in_g
 	return c;
 }
 B2_HD TileCoord tile_coord(const PassParams& P, uint64_t group, int tid) {
-	const int tpt = 1 << (P.k - 1);  // threads per tile
-	TileCoord c = tile_coord_of(P, group, tid / tpt);
-	c.t = tid % tpt;
+	TileCoord c = tile_coord_of(P, group, tid >> (P.k - 1));  // 2^(k-1) threads per tile
+	c.t = tid & ((1 << (P.k - 1)) - 1);
 	return c;
 }
 
@@ -211,23 +209,45 @@ B2_HD void copy16_s2g(uint32_t* g, const uint32_t* s) {
 }
 
 // chunk c of a group: piece = c & 7 (16 bytes of a line), then the tile (neighbouring lines in
-// memory), then the line x of the tile
+// memory), then the line x of the tile.  With k >= 4 a thread keeps its (piece, tile) and only
+// walks x, so the addresses advance by constant strides.
 template <bool STORE>
 B2_HD void group_copy(const PassParams& P, PassSmem& sm, uint64_t group, int tid) {
 	const int T = P.cta_threads;
-	const int tpg = (2 * T) >> P.k;
-#pragma unroll 4
-	for (int c = tid; c < 16 * T; c += T) {
-		const int piece = c & 7, r = c >> 3;
-		const int tig = r % tpg, x = r / tpg;
-		const TileCoord tc = tile_coord_of(P, group, tig);
-		if (!tc.active) continue;
-		uint32_t* s = &sm.slots[slot_word(tc.slot_base + x, piece * 4)];
-		const uint64_t off = line_of(P, tc, x) * 32 + piece * 4;
-		if (STORE)
-			copy16_s2g(P.dst + (uint64_t)tc.row * P.dst_row_words + off, s);
-		else
-			copy16_g2s(s, P.src + (uint64_t)(tc.row >> P.src_row_shift) * P.src_row_words + off);
+	const int ltpg = P.log_tpg, tpg = 1 << ltpg;
+	if (8 * tpg <= T) {
+		const int piece = tid & 7, r0 = tid >> 3;
+		const TileCoord tc = tile_coord_of(P, group, r0 & (tpg - 1));
+		if (tc.active) {
+			const int x0 = r0 >> ltpg, dx = T >> (3 + ltpg);
+			uint32_t* s = sm.slots + (tc.slot_base + x0) * kSlotWords + piece * 4;
+			const uint64_t off = line_of(P, tc, x0) * 32 + piece * 4;
+			const uint64_t gstep = ((uint64_t)dx << P.q0) * 32;
+			uint32_t* gd = P.dst + (uint64_t)tc.row * P.dst_row_words + off;
+			const uint32_t* gs = P.src + (uint64_t)(tc.row >> P.src_row_shift) * P.src_row_words + off;
+#pragma unroll 8
+			for (int it = 0; it < 16; it++) {
+				if (STORE)
+					copy16_s2g(gd, s);
+				else
+					copy16_g2s(s, gs);
+				s += dx * kSlotWords, gd += gstep, gs += gstep;
+			}
+		}
+	} else {
+#pragma unroll 1
+		for (int c = tid; c < 16 * T; c += T) {
+			const int piece = c & 7, r = c >> 3;
+			const int tig = r & (tpg - 1), x = r >> ltpg;
+			const TileCoord tc = tile_coord_of(P, group, tig);
+			if (!tc.active) continue;
+			uint32_t* s = &sm.slots[slot_word(tc.slot_base + x, piece * 4)];
+			const uint64_t off = line_of(P, tc, x) * 32 + piece * 4;
+			if (STORE)
+				copy16_s2g(P.dst + (uint64_t)tc.row * P.dst_row_words + off, s);
+			else
+				copy16_g2s(s, P.src + (uint64_t)(tc.row >> P.src_row_shift) * P.src_row_words + off);
+		}
 	}
 	if (!STORE) copy_wait_all();
 }

@@ -152,6 +152,8 @@ inline void plan_fill_pass(const HostPlan& hp, PassParams& P, int n, const uint3
 	P.inverse = inverse ? 1 : 0;
 	P.coset0 = inverse ? coset : 0;
 	P.cta_threads = hp.cta_threads;
+	P.log_tpg = 0;
+	while (((2 * hp.cta_threads) >> pd.k) >> (P.log_tpg + 1)) P.log_tpg++;
 	P.n_tiles = (uint64_t)rows << (hp.nb - pd.k);
 	const uint64_t tpg = (uint64_t)(2 * hp.cta_threads) >> pd.k;
 	P.n_groups = (P.n_tiles + tpg - 1) / tpg;

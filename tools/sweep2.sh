@@ -1,0 +1,14 @@
+#!/bin/bash
+# compare register-budget variants of the pass kernels (development aid)
+for W in 8 12 16; do
+ for T in 128 256; do
+  if [ $W = 8 ]; then unset B2NTT_LIB; else export B2NTT_LIB=$PWD/tools/variants/libb2ntt_w$W.so; fi
+  echo "== W=$W T=$T"
+  B2NTT_CTA_THREADS=$T python - <<'PY'
+import sys; sys.path.insert(0, '.')
+from tools.quick_time import time_plan
+for fb, lh in [(32, 28), (128, 24), (128, 28)]:
+    time_plan(fb, lh)
+PY
+ done
+done
