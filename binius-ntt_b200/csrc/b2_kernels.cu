@@ -20,7 +20,7 @@ namespace b2 {
 template <bool INV, int T>
 __global__ void __launch_bounds__(T, B2_WARPS_PER_SM * 32 / T) pass_kernel(const __grid_constant__ PassParams P) {
 	extern __shared__ __align__(16) uint32_t smem_raw[];
-	PassSmem sm = pass_smem_view(smem_raw, T);
+	PassSmem sm = pass_smem_view(smem_raw, P.group_lines);
 	const int tid = threadIdx.x;
 	pass_prologue(P, sm, tid);
 #pragma unroll 1
@@ -31,7 +31,8 @@ __global__ void __launch_bounds__(T, B2_WARPS_PER_SM * 32 / T) pass_kernel(const
 #pragma unroll 1
 		for (int step = 0; step < P.k; step++) {
 			const int i = pass_layer_bit(P, step);
-			pass_layer<INV>(P, sm, grp, tid, i, step == 0, step == P.k - 1);
+#pragma unroll 1
+			for (int vt = tid; vt < P.group_lines / 2; vt += T) pass_layer<INV>(P, sm, grp, vt, i, step == 0, step == P.k - 1);
 			__syncthreads();
 		}
 		group_copy<true>(P, sm, grp, tid);
@@ -42,7 +43,7 @@ __global__ void __launch_bounds__(T, B2_WARPS_PER_SM * 32 / T) pass_kernel(const
 template <bool INV, int T>
 static int launch_pass_t(const PassParams& P, cudaStream_t stream) {
 	int sms = 0;
-	const size_t smem = pass_smem_words(T, 1) * sizeof(uint32_t);
+	const size_t smem = pass_smem_words(P.group_lines, 1) * sizeof(uint32_t);
 	{
 		int dev = 0;
 		cudaGetDevice(&dev);

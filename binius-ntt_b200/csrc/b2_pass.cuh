@@ -59,6 +59,7 @@ struct PassParams {
 	int inverse;     // 0: forward, 1: inverse transform (layers in the opposite order)
 	int coset0;      // coset index of row 0 (inverse transform of one coset)
 	int cta_threads; // T
+	int group_lines; // G = 2 * T * (butterflies per thread per layer): lines a CTA holds at a time
 	int log_tpg;     // log2 of tiles per group = log2(2T) - k
 	uint64_t n_tiles;   // rows << (nb - k)
 	uint64_t n_groups;  // ceil(n_tiles / (2T >> k))
@@ -79,15 +80,15 @@ struct PassSmem {
 	uint32_t* inl_lo;   // [5][2T] in-line layers, by line x of the tile
 	uint32_t* inl_hi;   // [5][T]  in-line layers, by tile of the group
 };
-B2_HD size_t pass_smem_words(int T, int in_line) { return 160 + 2 * (size_t)T + T + 2 * kSlotWords * (size_t)T + (in_line ? 15 * (size_t)T : 0); }
-B2_HD PassSmem pass_smem_view(uint32_t* base, int T) {
+B2_HD size_t pass_smem_words(int G, int in_line) { return 160 + G + G / 2 + kSlotWords * (size_t)G + (in_line ? 5 * (size_t)G + 5 * (size_t)G / 2 : 0); }
+B2_HD PassSmem pass_smem_view(uint32_t* base, int G) {
 	PassSmem sm;
 	sm.slots = base;  // first: 16-byte aligned for the vector accesses
-	sm.lane_tw = sm.slots + 2 * kSlotWords * (size_t)T;
+	sm.lane_tw = sm.slots + kSlotWords * (size_t)G;
 	sm.tw_lo = sm.lane_tw + 160;
-	sm.tw_hi = sm.tw_lo + 2 * T;
-	sm.inl_lo = sm.tw_hi + T;
-	sm.inl_hi = sm.inl_lo + 10 * T;
+	sm.tw_hi = sm.tw_lo + G;
+	sm.inl_lo = sm.tw_hi + G / 2;
+	sm.inl_hi = sm.inl_lo + 5 * G;
 	return sm;
 }
 
@@ -126,7 +127,7 @@ B2_HD void pass_prologue(const PassParams& P, PassSmem& sm, int tid) {
 		const int L0 = P.n_inline;
 		for (int idx = tid; idx < L0 << P.k; idx += T) {
 			const int s = idx >> P.k, x = idx & ((1 << P.k) - 1);
-			sm.inl_lo[s * 2 * T + x] = xor_select64(P.consts + s * kConstPitch, (uint64_t)x << (L0 - 1 - s));
+			sm.inl_lo[s * P.group_lines + x] = xor_select64(P.consts + s * kConstPitch, (uint64_t)x << (L0 - 1 - s));
 		}
 	}
 }
@@ -142,7 +143,7 @@ struct TileCoord {
 
 B2_HD TileCoord tile_coord_of(const PassParams& P, uint64_t group, int tile_in_group) {
 	TileCoord c;
-	const uint64_t tile = group * (uint64_t)((2 * P.cta_threads) >> P.k) + tile_in_group;  // tiles per group = 2T >> k
+	const uint64_t tile = group * (uint64_t)(P.group_lines >> P.k) + tile_in_group;  // tiles per group = G >> k
 	c.tile_in_group = tile_in_group;
 	c.t = 0;
 	c.active = tile < P.n_tiles;
@@ -167,7 +168,7 @@ B2_HD uint64_t line_of(const PassParams& P, const TileCoord& c, int x) {
 // once per group: the tile-dependent part of every layer's twiddle
 B2_HD void group_prologue(const PassParams& P, PassSmem& sm, uint64_t group, int tid) {
 	const int T = P.cta_threads;
-	const int tpg = (2 * T) >> P.k;
+	const int tpg = P.group_lines >> P.k;
 	for (int idx = tid; idx < tpg * P.k; idx += T) {
 		const int tig = idx / P.k, i = idx % P.k;
 		const TileCoord c = tile_coord_of(P, group, tig);
@@ -181,7 +182,7 @@ B2_HD void group_prologue(const PassParams& P, PassSmem& sm, uint64_t group, int
 			const int tig = idx / L0, s = idx % L0;
 			const TileCoord c = tile_coord_of(P, group, tig);
 			const uint64_t ind = ((uint64_t)(P.coset0 + (c.row & P.coset_mask)) << (P.log_h - 1 - s)) | (c.hi << (P.k + L0 - 1 - s));
-			sm.inl_hi[s * T + tig] = c.active ? xor_select64(P.consts + s * kConstPitch, ind) : 0u;
+			sm.inl_hi[s * (P.group_lines / 2) + tig] = c.active ? xor_select64(P.consts + s * kConstPitch, ind) : 0u;
 		}
 	}
 }
@@ -219,14 +220,14 @@ B2_HD void group_copy(const PassParams& P, PassSmem& sm, uint64_t group, int tid
 		const int piece = tid & 7, r0 = tid >> 3;
 		const TileCoord tc = tile_coord_of(P, group, r0 & (tpg - 1));
 		if (tc.active) {
-			const int x0 = r0 >> ltpg, dx = T >> (3 + ltpg);
+			const int x0 = r0 >> ltpg, dx = T >> (3 + ltpg), nit = (8 * P.group_lines) / T;
 			uint32_t* s = sm.slots + (tc.slot_base + x0) * kSlotWords + piece * 4;
 			const uint64_t off = line_of(P, tc, x0) * 32 + piece * 4;
 			const uint64_t gstep = ((uint64_t)dx << P.q0) * 32;
 			uint32_t* gd = P.dst + (uint64_t)tc.row * P.dst_row_words + off;
 			const uint32_t* gs = P.src + (uint64_t)(tc.row >> P.src_row_shift) * P.src_row_words + off;
-#pragma unroll 8
-			for (int it = 0; it < 16; it++) {
+#pragma unroll 4
+			for (int it = 0; it < nit; it++) {
 				if (STORE)
 					copy16_s2g(gd, s);
 				else
@@ -236,7 +237,7 @@ B2_HD void group_copy(const PassParams& P, PassSmem& sm, uint64_t group, int tid
 		}
 	} else {
 #pragma unroll 1
-		for (int c = tid; c < 16 * T; c += T) {
+		for (int c = tid; c < 8 * P.group_lines; c += T) {
 			const int piece = c & 7, r = c >> 3;
 			const int tig = r & (tpg - 1), x = r >> ltpg;
 			const TileCoord tc = tile_coord_of(P, group, tig);
@@ -303,14 +304,14 @@ B2_HD void in_line_dispatch(int cls, uint32_t* A, uint32_t* B, int p, const uint
 // is uniform over the line (inl_hi ^ inl_lo), the lane part comes from lane_tw.
 template <bool INV>
 B2_HD void in_line_layers(const PassParams& P, const PassSmem& sm, Bundles& st, int tig, int xu, int xv) {
-	const int L0 = P.n_inline, T = P.cta_threads;
+	const int L0 = P.n_inline, G = P.group_lines;
 #pragma unroll 1
 	for (int n = 0; n < L0; n++) {
 		const int s = INV ? n : L0 - 1 - n;
 		const int p = s + P.lane_shift;
-		const uint32_t wh = sm.inl_hi[s * T + tig];
-		const uint32_t wa = wh ^ sm.inl_lo[s * 2 * T + xu];
-		const uint32_t wb = wh ^ sm.inl_lo[s * 2 * T + xv];
+		const uint32_t wh = sm.inl_hi[s * (G / 2) + tig];
+		const uint32_t wa = wh ^ sm.inl_lo[s * G + xu];
+		const uint32_t wb = wh ^ sm.inl_lo[s * G + xv];
 		in_line_dispatch<INV>(P.cls[s], st.A, st.B, p, &sm.lane_tw[s * 32], wa, wb);
 	}
 }

@@ -27,7 +27,8 @@ struct HostPlan {
 	int n_inline = 0, lane_shift = 0, batch_bits = 0, sliced_io = 0;
 	int nb = 0;          // line bits per row
 	bool tiny = false;   // fewer than two lines of butterfly work per row: element-wise kernels
-	int cta_threads = 128;  // T: a CTA holds 2T lines; at most log2(2T) line layers per pass
+	int cta_threads = 128;  // T threads per CTA
+	int group_lines = 512;  // G lines a CTA holds at a time (G / 2T butterflies per thread per layer); <= log2(G) line layers per pass
 	uint32_t consts[32 * kConstPitch];
 	uint32_t lane_tw[5 * 32];
 	uint8_t cls[32];
@@ -73,7 +74,7 @@ inline int twiddle_class(uint32_t or_of_values) {
 	return 5;
 }
 
-inline int plan_build(HostPlan& hp, int field_bits, int layout, int log_h, int log_rate, int batch, int cta_threads = 0) {
+inline int plan_build(HostPlan& hp, int field_bits, int layout, int log_h, int log_rate, int batch, int cta_threads = 0, int group_lines = 0) {
 	if (!plan_args_ok(field_bits, layout, log_h, log_rate, batch)) return -1;
 	hp.field_bits = field_bits, hp.layout = layout, hp.log_h = log_h, hp.log_rate = log_rate, hp.batch = batch;
 	hp.limbs_log = field_bits == 128 ? 2 : 0;
@@ -85,8 +86,11 @@ inline int plan_build(HostPlan& hp, int field_bits, int layout, int log_h, int l
 	hp.nb = log_h + hp.limbs_log - 5;
 	if (cta_threads != 64 && cta_threads != 128 && cta_threads != 256) cta_threads = 128;
 	hp.cta_threads = cta_threads;
+	if (group_lines != 128 && group_lines != 256 && group_lines != 512) group_lines = 512;
+	if (group_lines < 2 * cta_threads) group_lines = 2 * cta_threads;
+	hp.group_lines = group_lines;
 	int max_bits = 0;
-	while ((1 << max_bits) < 2 * cta_threads) max_bits++;
+	while ((1 << max_bits) < group_lines) max_bits++;
 	plan_constants(log_h, log_rate, hp.consts);
 	for (int s = 0; s < 32; s++) {
 		uint32_t m = 0;
@@ -152,10 +156,11 @@ inline void plan_fill_pass(const HostPlan& hp, PassParams& P, int n, const uint3
 	P.inverse = inverse ? 1 : 0;
 	P.coset0 = inverse ? coset : 0;
 	P.cta_threads = hp.cta_threads;
+	P.group_lines = hp.group_lines;
 	P.log_tpg = 0;
-	while (((2 * hp.cta_threads) >> pd.k) >> (P.log_tpg + 1)) P.log_tpg++;
+	while ((hp.group_lines >> pd.k) >> (P.log_tpg + 1)) P.log_tpg++;
 	P.n_tiles = (uint64_t)rows << (hp.nb - pd.k);
-	const uint64_t tpg = (uint64_t)(2 * hp.cta_threads) >> pd.k;
+	const uint64_t tpg = (uint64_t)hp.group_lines >> pd.k;
 	P.n_groups = (P.n_tiles + tpg - 1) / tpg;
 	memcpy(P.cls, hp.cls, 32);
 }

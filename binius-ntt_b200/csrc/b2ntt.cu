@@ -53,7 +53,9 @@ extern "C" int b2ntt_plan_create(b2ntt_plan** out, int field_bits, int layout, i
 	if (!p) return B2NTT_ENOMEM;
 	int cta = 0;
 	if (const char* e = getenv("B2NTT_CTA_THREADS")) cta = atoi(e);  // tuning knob: 64, 128 or 256
-	if (plan_build(p->hp, field_bits, layout, log_h, log_rate, batch, cta)) {
+	int glines = 0;
+	if (const char* e = getenv("B2NTT_GROUP_LINES")) glines = atoi(e);  // tuning knob: 128, 256 or 512
+	if (plan_build(p->hp, field_bits, layout, log_h, log_rate, batch, cta, glines)) {
 		delete p;
 		return B2NTT_EINVAL;
 	}

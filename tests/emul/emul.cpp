@@ -15,24 +15,24 @@ using namespace b2;
 template <bool INV>
 static void run_pass(const PassParams& P) {
 	const int T = P.cta_threads;
-	std::vector<uint32_t> mem(pass_smem_words(T, 1));
-	PassSmem sm = pass_smem_view(mem.data(), T);
+	std::vector<uint32_t> mem(pass_smem_words(P.group_lines, 1));
+	PassSmem sm = pass_smem_view(mem.data(), P.group_lines);
 	for (int t = 0; t < T; t++) pass_prologue(P, sm, t);
 	for (uint64_t grp = 0; grp < P.n_groups; grp++) {
 		for (int t = 0; t < T; t++) group_prologue(P, sm, grp, t);
 		for (int t = 0; t < T; t++) group_copy<false>(P, sm, grp, t);
 		for (int step = 0; step < P.k; step++) {
 			const int i = pass_layer_bit(P, step);
-			for (int t = 0; t < T; t++) pass_layer<INV>(P, sm, grp, t, i, step == 0, step == P.k - 1);
+			for (int t = 0; t < P.group_lines / 2; t++) pass_layer<INV>(P, sm, grp, t, i, step == 0, step == P.k - 1);
 		}
 		for (int t = 0; t < T; t++) group_copy<true>(P, sm, grp, t);
 	}
 }
 
 extern "C" int emul_antt_cta(int field_bits, int layout, int log_h, int log_rate, int batch, const uint32_t* in,
-                             uint32_t* out, int inverse, int coset, int cta_threads) {
+                             uint32_t* out, int inverse, int coset, int cta_threads, int group_lines) {
 	HostPlan hp;
-	if (plan_build(hp, field_bits, layout, log_h, log_rate, batch, cta_threads)) return -1;
+	if (plan_build(hp, field_bits, layout, log_h, log_rate, batch, cta_threads, group_lines)) return -1;
 	if (hp.tiny) return -4;
 	PassParams P;
 	const int np = (int)hp.passes.size();
@@ -44,7 +44,7 @@ extern "C" int emul_antt_cta(int field_bits, int layout, int log_h, int log_rate
 }
 extern "C" int emul_antt(int field_bits, int layout, int log_h, int log_rate, int batch, const uint32_t* in,
                          uint32_t* out, int inverse, int coset) {
-	return emul_antt_cta(field_bits, layout, log_h, log_rate, batch, in, out, inverse, coset, 0);
+	return emul_antt_cta(field_bits, layout, log_h, log_rate, batch, in, out, inverse, coset, 0, 0);
 }
 
 extern "C" int emul_plan_passes(int field_bits, int layout, int log_h, int log_rate, int* q0, int* k, int* in_line,

@@ -1,6 +1,6 @@
 #!/bin/bash
 # compare register-budget variants of the pass kernels (development aid)
-for W in 8 12 16; do
+for W in 8 12; do
  for T in 128 256; do
   if [ $W = 8 ]; then unset B2NTT_LIB; else export B2NTT_LIB=$PWD/tools/variants/libb2ntt_w$W.so; fi
   echo "== W=$W T=$T"
