@@ -19,3 +19,4 @@ from .api import (  # noqa: F401
     mul,
     mul_repeat,
 )
+from .multi import ColumnShardedRS, FourStepNTT, shard_columns  # noqa: F401

@@ -38,6 +38,8 @@ def lib():
         L.b2ntt_exec.argtypes = [vp, vp, vp, vp]
         L.b2ntt_exec_inverse.argtypes = [vp, vp, vp, i, vp]
         L.b2ntt_exec_host.argtypes = [vp, vp, sz, vp]
+        L.b2ntt_exec_coset.argtypes = [vp, vp, vp, i, vp]
+        L.b2ntt_exec_top.argtypes = [vp, vp, i, vp]
         L.b2ntt_plan_launches.argtypes = [vp]
         L.b2ntt_plan_passes.argtypes = [vp]
         L.b2ntt_plan_constants.argtypes = [vp, vp]
@@ -128,6 +130,21 @@ class Plan:
         self._dev_ok(d_out, self.in_words, "d_out")
         _check(lib().b2ntt_exec_inverse(self._h, d_in.data_ptr(), d_out.data_ptr(), coset, _stream_ptr(stream)), "b2ntt_exec_inverse")
         return d_out
+
+    def exec_coset(self, d_in, d_out=None, coset=0, stream=None):
+        """Forward transform of ONE coset row (row `coset` of exec's output); in place by default."""
+        self._dev_ok(d_in, self.in_words, "d_in")
+        if d_out is None:
+            d_out = d_in
+        self._dev_ok(d_out, self.in_words, "d_out")
+        _check(lib().b2ntt_exec_coset(self._h, d_in.data_ptr(), d_out.data_ptr(), coset, _stream_ptr(stream)), "b2ntt_exec_coset")
+        return d_out
+
+    def exec_top(self, d_buf, log_segments, stream=None):
+        """Top `log_segments` stages of this (full) transform on one device's segments, in place."""
+        self._dev_ok(d_buf, self.in_words >> log_segments, "d_buf")
+        _check(lib().b2ntt_exec_top(self._h, d_buf.data_ptr(), log_segments, _stream_ptr(stream)), "b2ntt_exec_top")
+        return d_buf
 
     def exec_host(self, h_in, h_out=None):
         """Host numpy (or pinned torch CPU tensor) in -> host out: H2D + transform + D2H + sync."""

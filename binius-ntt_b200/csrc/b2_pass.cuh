@@ -57,7 +57,8 @@ struct PassParams {
 	int k;           // line bits fused in this pass (1..log2(2T))
 	int in_line;     // 1: also run the layers inside a line (the pass with q0 == batch_bits)
 	int inverse;     // 0: forward, 1: inverse transform (layers in the opposite order)
-	int coset0;      // coset index of row 0 (inverse transform of one coset)
+	int coset0;      // coset index of row 0 (inverse transform of one coset, forward transform of one coset)
+	int stage_shift; // added to the local stage number when looking up constants and classes (top phase of a split transform)
 	int cta_threads; // T
 	int group_lines; // G = 2 * T * (butterflies per thread per layer): lines a CTA holds at a time
 	int log_tpg;     // log2 of tiles per group = log2(2T) - k
@@ -106,7 +107,7 @@ B2_HD uint32_t xor_select64(const uint32_t* table, uint64_t bits) {
 	return w;
 }
 
-B2_HD int pass_stage(const PassParams& P, int i) { return P.n_inline + P.q0 - P.batch_bits + i; }
+B2_HD int pass_stage(const PassParams& P, int i) { return P.n_inline + P.q0 - P.batch_bits + i + P.stage_shift; }
 
 // once per CTA: tile-independent twiddle tables
 B2_HD void pass_prologue(const PassParams& P, PassSmem& sm, int tid) {

@@ -133,19 +133,20 @@ inline int plan_build(HostPlan& hp, int field_bits, int layout, int log_h, int l
 // reverse).  consts / lane_tw point to wherever the kernels will read the tables (device memory on
 // the GPU, hp's own arrays in the CPU emulation).  Intermediate passes leave the lines bit-sliced.
 inline void plan_fill_pass(const HostPlan& hp, PassParams& P, int n, const uint32_t* src, uint32_t* dst, const uint32_t* consts,
-                           const uint32_t* lane_tw, bool inverse, int coset) {
+                           const uint32_t* lane_tw, bool inverse, int coset, bool one_coset = false) {
 	const int np = (int)hp.passes.size();
 	const PassDesc& pd = inverse ? hp.passes[np - 1 - n] : hp.passes[n];
 	memset(&P, 0, sizeof P);
 	const uint64_t row_words = (uint64_t)32 << hp.nb;
-	const int rows = inverse ? hp.batch : hp.batch << hp.log_rate;
+	const bool single = inverse || one_coset;  // rows are columns of ONE coset
+	const int rows = single ? hp.batch : hp.batch << hp.log_rate;
 	const bool first_pass = n == 0, last_pass = n == np - 1;
 	P.src = first_pass ? src : dst;
 	P.dst = dst;
 	P.src_row_words = row_words;
 	P.dst_row_words = row_words;
-	P.src_row_shift = (first_pass && !inverse) ? hp.log_rate : 0;
-	P.coset_mask = inverse ? 0u : ((1u << hp.log_rate) - 1);
+	P.src_row_shift = (first_pass && !single) ? hp.log_rate : 0;
+	P.coset_mask = single ? 0u : ((1u << hp.log_rate) - 1);
 	P.consts = consts;
 	P.lane_tw = lane_tw;
 	P.log_h = hp.log_h, P.log_rate = hp.log_rate, P.limbs_log = hp.limbs_log;
@@ -154,7 +155,7 @@ inline void plan_fill_pass(const HostPlan& hp, PassParams& P, int n, const uint3
 	P.dst_sliced = (hp.sliced_io || !last_pass) ? 1 : 0;
 	P.nb = hp.nb, P.q0 = pd.q0, P.k = pd.k, P.in_line = pd.in_line;
 	P.inverse = inverse ? 1 : 0;
-	P.coset0 = inverse ? coset : 0;
+	P.coset0 = single ? coset : 0;
 	P.cta_threads = hp.cta_threads;
 	P.group_lines = hp.group_lines;
 	P.log_tpg = 0;
@@ -163,6 +164,37 @@ inline void plan_fill_pass(const HostPlan& hp, PassParams& P, int n, const uint3
 	const uint64_t tpg = (uint64_t)hp.group_lines >> pd.k;
 	P.n_groups = (P.n_tiles + tpg - 1) / tpg;
 	memcpy(P.cls, hp.cls, 32);
+}
+
+// Top phase of a transform split over 2^log_seg devices: the buffer holds
+// 2^log_seg segments of 2^(log_h - 2*log_seg) elements each; segment h is the
+// slice (h, m, .) of the global index (h: top log_seg bits, m: this device).  Runs the top log_seg
+// stages (global stages log_h-1 .. log_h-log_seg) in place, element-wise across the segments: their
+// twiddles depend only on the h bits above the butterfly bit, which the local index keeps on top.
+// hp is the plan of the FULL transform (log_rate 0, compact or bit-sliced images).  Returns 0 or -1.
+inline int plan_fill_top(const HostPlan& hp, PassParams& P, int log_seg, uint32_t* buf, const uint32_t* consts, const uint32_t* lane_tw) {
+	if (hp.log_rate != 0 || log_seg < 1 || log_seg > 4) return -1;
+	const int nb_local = hp.nb - log_seg;                     // line bits of the local buffer
+	const int q0 = nb_local - log_seg;                        // the segment-index bits are its top bits
+	if (q0 < hp.batch_bits) return -1;                        // a segment is at least one line
+	memset(&P, 0, sizeof P);
+	const uint64_t row_words = (uint64_t)32 << nb_local;
+	P.src = buf, P.dst = buf;
+	P.src_row_words = P.dst_row_words = row_words;
+	P.consts = consts, P.lane_tw = lane_tw;
+	P.log_h = hp.log_h, P.log_rate = 0, P.limbs_log = hp.limbs_log;
+	P.n_inline = hp.n_inline, P.lane_shift = hp.lane_shift, P.batch_bits = hp.batch_bits;
+	P.src_sliced = hp.sliced_io, P.dst_sliced = hp.sliced_io;
+	P.nb = nb_local, P.q0 = q0, P.k = log_seg, P.in_line = 0;
+	P.stage_shift = log_seg;
+	P.cta_threads = hp.cta_threads;
+	P.group_lines = hp.group_lines;
+	while ((hp.group_lines >> log_seg) >> (P.log_tpg + 1)) P.log_tpg++;
+	P.n_tiles = (uint64_t)hp.batch << (nb_local - log_seg);
+	const uint64_t tpg = (uint64_t)hp.group_lines >> log_seg;
+	P.n_groups = (P.n_tiles + tpg - 1) / tpg;
+	memcpy(P.cls, hp.cls, 32);
+	return 0;
 }
 
 }  // namespace b2

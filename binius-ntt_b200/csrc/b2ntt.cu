@@ -86,10 +86,11 @@ extern "C" int b2ntt_plan_destroy(b2ntt_plan* p) {
 	return B2NTT_OK;
 }
 
-static int run(b2ntt_plan* p, const void* d_in, void* d_out, bool inverse, int coset, cudaStream_t st) {
+static int run(b2ntt_plan* p, const void* d_in, void* d_out, bool inverse, int coset, cudaStream_t st, bool one_coset = false) {
 	const HostPlan& hp = p->hp;
 	if (!d_in || !d_out) return B2NTT_EINVAL;
-	if (d_in == d_out && hp.log_rate != 0 && !inverse) return B2NTT_EINVAL;
+	const bool single = inverse || one_coset;
+	if (d_in == d_out && hp.log_rate != 0 && !single) return B2NTT_EINVAL;
 	CU(cudaSetDevice(p->device));
 	const uint32_t* src = (const uint32_t*)d_in;
 	uint32_t* dst = (uint32_t*)d_out;
@@ -98,10 +99,10 @@ static int run(b2ntt_plan* p, const void* d_in, void* d_out, bool inverse, int c
 		memset(&T, 0, sizeof T);
 		T.src = src, T.dst = dst, T.consts = p->d_consts;
 		T.log_h = hp.log_h, T.log_rate = hp.log_rate, T.limbs_log = hp.limbs_log;
-		T.rows = inverse ? hp.batch : hp.batch << hp.log_rate;
-		T.src_row_shift = inverse ? 0 : hp.log_rate;
-		T.coset_mask = inverse ? 0u : ((1u << hp.log_rate) - 1);
-		T.coset0 = inverse ? (uint32_t)coset : 0u;
+		T.rows = single ? hp.batch : hp.batch << hp.log_rate;
+		T.src_row_shift = single ? 0 : hp.log_rate;
+		T.coset_mask = single ? 0u : ((1u << hp.log_rate) - 1);
+		T.coset0 = single ? (uint32_t)coset : 0u;
 		T.inverse = inverse ? 1 : 0;
 		if (launch_tiny_fanout(T, st)) return cuda_fail(cudaGetLastError(), "tiny_fanout");
 		const uint64_t words = (uint64_t)T.rows << (hp.log_h + hp.limbs_log);
@@ -116,7 +117,7 @@ static int run(b2ntt_plan* p, const void* d_in, void* d_out, bool inverse, int c
 	PassParams P;
 	const int np = (int)hp.passes.size();
 	for (int n = 0; n < np; n++) {
-		plan_fill_pass(hp, P, n, src, dst, p->d_consts, p->d_lane_tw, inverse, coset);
+		plan_fill_pass(hp, P, n, src, dst, p->d_consts, p->d_lane_tw, inverse, coset, one_coset);
 		if (launch_pass(P, st)) return cuda_fail(cudaGetLastError(), "launch_pass");
 	}
 	return B2NTT_OK;
@@ -131,6 +132,21 @@ extern "C" int b2ntt_exec_inverse(b2ntt_plan* p, const void* d_in, void* d_out, 
 	if (!p) return B2NTT_EINVAL;
 	if (coset < 0 || coset >= (1 << p->hp.log_rate)) return B2NTT_EINVAL;
 	return run(p, d_in, d_out, true, coset, (cudaStream_t)stream);
+}
+
+extern "C" int b2ntt_exec_coset(b2ntt_plan* p, const void* d_in, void* d_out, int coset, void* stream) {
+	if (!p) return B2NTT_EINVAL;
+	if (coset < 0 || coset >= (1 << p->hp.log_rate)) return B2NTT_EINVAL;
+	return run(p, d_in, d_out, false, coset, (cudaStream_t)stream, true);
+}
+
+extern "C" int b2ntt_exec_top(b2ntt_plan* p, void* d_buf, int log_segments, void* stream) {
+	if (!p || !d_buf) return B2NTT_EINVAL;
+	PassParams P;
+	if (p->hp.tiny || plan_fill_top(p->hp, P, log_segments, (uint32_t*)d_buf, p->d_consts, p->d_lane_tw)) return B2NTT_EINVAL;
+	CU(cudaSetDevice(p->device));
+	if (launch_pass(P, (cudaStream_t)stream)) return cuda_fail(cudaGetLastError(), "launch_pass");
+	return B2NTT_OK;
 }
 
 extern "C" int b2ntt_exec_host(b2ntt_plan* p, const void* h_in, size_t n_in, void* h_out) {

@@ -65,6 +65,20 @@ int b2ntt_exec(b2ntt_plan* plan, const void* d_in, void* d_out, void* stream);
  * d_in = batch * 2^log_h evaluations on coset `coset`, d_out = batch * 2^log_h coefficients. */
 int b2ntt_exec_inverse(b2ntt_plan* plan, const void* d_in, void* d_out, int coset, void* stream);
 
+/* Forward transform of ONE coset row per column: d_in = batch * 2^log_h coefficients, d_out = batch *
+ * 2^log_h evaluations on coset `coset` (0 <= coset < 2^log_rate) -- row `coset` of b2ntt_exec's output.
+ * No reference counterpart (the reference always produces every coset, additive_ntt.cuh:213-215); this
+ * is phase 2 of a transform split over several devices: device h of 2^g runs coset h of a
+ * (log_h - g, log_rate = g) plan on the block it owns.  d_out may equal d_in. */
+int b2ntt_exec_coset(b2ntt_plan* plan, const void* d_in, void* d_out, int coset, void* stream);
+
+/* Phase 1 of a transform split over 2^log_segments devices: `plan` describes the
+ * FULL transform (log_rate 0); d_buf holds this device's 2^log_segments segments of
+ * 2^(log_h - 2*log_segments) elements, segment h = global indices (h, m = this device, .).  Runs the top
+ * log_segments butterfly stages (additive_ntt.cuh:127-159 for stages log_h-1 .. log_h-log_segments) in
+ * place; their twiddles depend only on the h bits above the butterfly bit.  1 <= log_segments <= 4. */
+int b2ntt_exec_top(b2ntt_plan* plan, void* d_buf, int log_segments, void* stream);
+
 /* Replaces bool AdditiveNTT::apply(const NTTData&, NTTData&) (additive_ntt.cuh:201-265): host input,
  * host output, H2D + transform + D2H + synchronise on the plan's own stream.  n_in is the input
  * element count per column and must equal 2^log_h (else B2NTT_EINVAL, apply()'s `return false`). */
