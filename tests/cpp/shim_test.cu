@@ -1,0 +1,155 @@
+// shim_test.cu -- C++ parity test of the drop-in surface include/ulvt/... over libb2ntt.so.
+// TEST CODE.  It reads like the reference's own tests (ntt/tests/test_ntt.cu:191-217 additive cases,
+// finite_fields/tests/test_fanpaartower.cu, tests.cu) with Catch2 replaced by a small CHECK macro,
+// and uses the oracle (oracle/oracle.h: golden MD5 table, MD5, CPU field restatement) as checker.
+//   usage: shim_test [max_log_h_r0 [max_log_h_r2]]     exit code 0 = all checks passed
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstring>
+#include <random>
+#include <vector>
+
+#include "../../oracle/oracle.h"
+#include "ulvt/finite_fields/binary_tower.cuh"
+#include "ulvt/finite_fields/circuit_generator/unrolled/binary_tower_unrolled.cuh"
+#include "ulvt/ntt/additive_ntt.cuh"
+#include "ulvt/utils/bitslicing.cuh"
+
+static int g_failed = 0, g_checks = 0;
+#define CHECK(cond)                                                          \
+	do {                                                                     \
+		g_checks++;                                                          \
+		if (!(cond)) {                                                       \
+			g_failed++;                                                      \
+			printf("CHECK failed %s:%d: %s\n", __FILE__, __LINE__, #cond);   \
+		}                                                                    \
+	} while (0)
+
+// test_ntt.cu:191-217
+static bool run_and_check_additive_ntt(int log_h, int log_rate) {
+	std::mt19937 gen(0xdeadbeef + log_h + log_rate);
+	const size_t inp_size = (size_t)1 << log_h, out_size = (size_t)1 << (log_h + log_rate);
+	NTTData<uint32_t> ntt_inp(DataOrder::IN_ORDER, inp_size);
+	for (size_t i = 0; i < inp_size; i++) ntt_inp.data[i] = gen();
+	AdditiveNTTConf<uint32_t, FanPaarTowerField<5>> nttconf(log_h, log_rate);
+	AdditiveNTT<uint32_t, FanPaarTowerField<5>> add_ntt(nttconf);
+	NTTData<uint32_t> ntt_out(out_size);
+	if (!add_ntt.apply(ntt_inp, ntt_out)) return false;
+	char hex[33];
+	orc_md5_hex(ntt_out.data.get(), ntt_out.byte_len(), hex);
+	const char* want = orc_golden_md5(log_rate, log_h);
+	return want && strcmp(hex, want) == 0 && ntt_out.order == DataOrder::IN_ORDER;
+}
+
+// limb l of a GF(2^128) transform is the GF(2^32) transform of limb l: limb 0 carries the reference stream
+static bool run_and_check_additive_ntt128(int log_h, int log_rate) {
+	std::mt19937 gen(0xdeadbeef + log_h + log_rate), other(12345 + log_h);
+	const size_t inp_size = (size_t)1 << log_h, out_size = (size_t)1 << (log_h + log_rate);
+	NTTData<b128> in(DataOrder::IN_ORDER, inp_size);
+	for (size_t i = 0; i < inp_size; i++) {
+		in.data[i].w[0] = gen();
+		for (int l = 1; l < 4; l++) in.data[i].w[l] = other();
+	}
+	AdditiveNTTConf<b128, FanPaarTowerField<7>> conf(log_h, log_rate);
+	AdditiveNTT<b128, FanPaarTowerField<7>> ntt(conf);
+	NTTData<b128> out(out_size);
+	if (!ntt.apply(in, out)) return false;
+	std::vector<uint32_t> limb0(out_size);
+	for (size_t i = 0; i < out_size; i++) limb0[i] = out.data[i].w[0];
+	char hex[33];
+	orc_md5_hex(limb0.data(), limb0.size() * 4, hex);
+	const char* want = orc_golden_md5(log_rate, log_h);
+	return want && strcmp(hex, want) == 0;
+}
+
+template <int H>
+__global__ void mul_unrolled_kernel(const uint32_t* a, const uint32_t* b, uint32_t* o) {
+	multiply_unrolled<H>(a + (size_t)threadIdx.x * (1 << H), b + (size_t)threadIdx.x * (1 << H), o + (size_t)threadIdx.x * (1 << H));
+}
+
+template <int H>
+static void check_unrolled_on_device(std::mt19937& gen) {
+	constexpr int N = 1 << H, T = 8;
+	std::vector<uint32_t> a(N * T), b(N * T), got(N * T), want(N * T);
+	for (auto& x : a) x = gen();
+	for (auto& x : b) x = gen();
+	for (int t = 0; t < T; t++) orc_mul_bitsliced(&a[t * N], &b[t * N], &want[t * N], H);
+	uint32_t *da, *db;
+	cudaMalloc(&da, N * T * 4), cudaMalloc(&db, N * T * 4);
+	cudaMemcpy(da, a.data(), N * T * 4, cudaMemcpyHostToDevice);
+	cudaMemcpy(db, b.data(), N * T * 4, cudaMemcpyHostToDevice);
+	mul_unrolled_kernel<H><<<1, T>>>(da, db, da);  // destination aliases an input (core.cu:21)
+	cudaMemcpy(got.data(), da, N * T * 4, cudaMemcpyDeviceToHost);
+	CHECK(cudaGetLastError() == cudaSuccess);
+	CHECK(got == want);
+	std::vector<uint32_t> host(N);
+	multiply_unrolled<H>(a.data(), b.data(), host.data());
+	CHECK(memcmp(host.data(), want.data(), N * 4) == 0);
+	cudaFree(da), cudaFree(db);
+}
+
+int main(int argc, char** argv) {
+	const int max_r0 = argc > 1 ? atoi(argv[1]) : 24, max_r2 = argc > 2 ? atoi(argv[2]) : 22;
+	CHECK(check_gpu_capabilities());  // test_ntt.cu:189
+
+	// ---- additive NTT against the reference's golden digests (test_ntt.cu:52-124) ----
+	for (int log_h = 1; log_h <= max_r0; log_h++) CHECK(run_and_check_additive_ntt(log_h, 0));
+	for (int log_h = 1; log_h <= max_r2; log_h++) CHECK(run_and_check_additive_ntt(log_h, 2));
+	for (int log_h : {3, 9, 16, 20}) CHECK(run_and_check_additive_ntt128(log_h, 0));
+	CHECK(run_and_check_additive_ntt128(14, 2));
+	{  // apply(): false on wrong size / order, nothing else (additive_ntt.cuh:206-208)
+		AdditiveNTTConf<uint32_t, FanPaarTowerField<5>> conf(10, 0);
+		AdditiveNTT<uint32_t, FanPaarTowerField<5>> ntt(conf);
+		NTTData<uint32_t> bad_size(DataOrder::IN_ORDER, 1000), bad_order(DataOrder::BIT_REVERSED, 1024), out(1024);
+		CHECK(!ntt.apply(bad_size, out));
+		CHECK(!ntt.apply(bad_order, out));
+	}
+
+	// ---- compact tower field against the oracle (test_fanpaartower.cu:55-120 style) ----
+	std::mt19937 gen(2024);
+	for (int i = 0; i < 2000; i++) {
+		const uint32_t a = gen(), b = gen();
+		CHECK(FanPaarTowerField<5>::multiply(a, b) == orc_mul32(a, b));
+		CHECK(FanPaarTowerField<5>::square(a) == orc_mul32(a, a));
+		if (a) CHECK(FanPaarTowerField<5>::multiply(a, FanPaarTowerField<5>::inverse(a)) == 1u);
+		CHECK(FanPaarTowerField<4>::multiply(a & 0xffff, b & 0xffff) == orc_mul32(a & 0xffff, b & 0xffff));
+		CHECK(FanPaarTowerField<3>::multiply(a & 0xff, b & 0xff) == orc_mul32(a & 0xff, b & 0xff));
+		const uint32_t r[6] = {(uint32_t)gen(), (uint32_t)gen(), (uint32_t)gen(), (uint32_t)gen(), (uint32_t)gen(), (uint32_t)gen()};
+		b128 x{{a, b, r[0], r[1]}}, y{{r[2], r[3], r[4], r[5]}}, z = FanPaarTowerField<7>::multiply(x, y);
+		uint32_t w[4];
+		orc_mul128_words(x.w, y.w, w);
+		CHECK(memcmp(z.w, w, 16) == 0);
+	}
+	CHECK(FanPaarTowerField<5>::N_BITS() == 32 && FanPaarTowerField<3>::is_valid(0xff) && !FanPaarTowerField<3>::is_valid(0x100));
+
+	// ---- bit-slicing and the bit-sliced products (tests.cu:125-201, test_fanpaartower.cu:127-273 style) ----
+	{
+		std::array<uint32_t, 128> blk, ref;
+		for (auto& x : blk) x = gen();
+		ref = blk;
+		orc_bitslice(ref.data(), 128);
+		BitsliceUtils<128> u(blk);
+		u.bitslice_transpose();
+		CHECK(blk == ref);
+		uint32_t* d;
+		std::array<uint32_t, 128> dev = ref;
+		cudaMalloc(&d, 512);
+		cudaMemcpy(d, dev.data(), 512, cudaMemcpyHostToDevice);
+		untranspose_kernel<128><<<1, 32>>>(d, 1);
+		cudaMemcpy(dev.data(), d, 512, cudaMemcpyDeviceToHost);
+		BitsliceUtils<128>::bitslice_untranspose(blk.data());
+		CHECK(dev == blk);
+		CHECK(bitslice_device<128>(d, 1));
+		cudaMemcpy(dev.data(), d, 512, cudaMemcpyDeviceToHost);
+		CHECK(dev == ref);
+		cudaFree(d);
+	}
+	check_unrolled_on_device<2>(gen);
+	check_unrolled_on_device<5>(gen);
+	check_unrolled_on_device<6>(gen);
+	check_unrolled_on_device<7>(gen);
+
+	printf("shim_test: %d checks, %d failed\n", g_checks, g_failed);
+	return g_failed ? 1 : 0;
+}
