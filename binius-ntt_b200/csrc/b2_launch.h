@@ -7,6 +7,7 @@
 namespace b2 {
 
 struct PassParams;
+struct UpperParams;
 
 // element-wise path for transforms with fewer than two 128-byte lines per row
 struct TinyParams {
@@ -22,6 +23,7 @@ struct TinyParams {
 };
 
 int launch_pass(const PassParams& P, cudaStream_t stream);
+int launch_upper(const UpperParams& U, cudaStream_t stream);  // b2_upper.cu
 int launch_tiny_fanout(const TinyParams& T, cudaStream_t stream);
 int launch_tiny_layers(const TinyParams& T, cudaStream_t stream);
 

@@ -12,6 +12,7 @@
 #include <vector>
 
 #include "b2_pass.cuh"
+#include "b2_upper.cuh"
 
 namespace b2 {
 
@@ -19,6 +20,7 @@ struct PassDesc {
 	int q0;       // first line bit
 	int k;        // line bits fused
 	int in_line;  // run the in-line layers in this pass
+	int kind;     // 0: bundle pass through shared memory (b2_pass.cuh), 1: upper pass with warp-uniform twiddles (b2_upper.cuh)
 };
 
 struct HostPlan {
@@ -74,7 +76,8 @@ inline int twiddle_class(uint32_t or_of_values) {
 	return 5;
 }
 
-inline int plan_build(HostPlan& hp, int field_bits, int layout, int log_h, int log_rate, int batch, int cta_threads = 0, int group_lines = 0) {
+inline int plan_build(HostPlan& hp, int field_bits, int layout, int log_h, int log_rate, int batch, int cta_threads = 0, int group_lines = 0,
+                      int use_upper = 1) {
 	if (!plan_args_ok(field_bits, layout, log_h, log_rate, batch)) return -1;
 	hp.field_bits = field_bits, hp.layout = layout, hp.log_h = log_h, hp.log_rate = log_rate, hp.batch = batch;
 	hp.limbs_log = field_bits == 128 ? 2 : 0;
@@ -109,7 +112,22 @@ inline int plan_build(HostPlan& hp, int field_bits, int layout, int log_h, int l
 	const int nbf = hp.nb - hp.batch_bits;  // butterfly line bits
 	hp.passes.clear();
 	hp.tiny = nbf < 1;
-	if (!hp.tiny) {
+	if (!hp.tiny && use_upper && nbf > max_bits && max_bits >= 6) {
+		// lowest pass: the bundle pass with the in-line layers (8 or 9 line bits); everything above it
+		// has strides >= 32 lines and runs as upper passes of 4 (or 2) line bits, highest first
+		int kb = max_bits;
+		if ((nbf - kb) & 1) kb--;
+		int left = nbf - kb, q = hp.batch_bits + nbf;
+		if (left & 3) {
+			q -= 2, left -= 2;
+			hp.passes.push_back(PassDesc{q, 2, 0, 1});
+		}
+		while (left > 0) {
+			q -= 4, left -= 4;
+			hp.passes.push_back(PassDesc{q, 4, 0, 1});
+		}
+		hp.passes.push_back(PassDesc{hp.batch_bits, kb, 1, 0});
+	} else if (!hp.tiny) {
 		const int np = (nbf + max_bits - 1) / max_bits;
 		// the lowest pass also runs the in-line layers, so it gets the smallest share of line bits
 		int left = nbf;
@@ -123,7 +141,7 @@ inline int plan_build(HostPlan& hp, int field_bits, int layout, int log_h, int l
 		int q = hp.batch_bits + nbf;
 		for (int p = np - 1; p >= 0; p--) {
 			q -= ks[p];
-			hp.passes.push_back(PassDesc{q, ks[p], p == 0 ? 1 : 0});
+			hp.passes.push_back(PassDesc{q, ks[p], p == 0 ? 1 : 0, 0});
 		}
 	}
 	return 0;
@@ -164,6 +182,32 @@ inline void plan_fill_pass(const HostPlan& hp, PassParams& P, int n, const uint3
 	const uint64_t tpg = (uint64_t)hp.group_lines >> pd.k;
 	P.n_groups = (P.n_tiles + tpg - 1) / tpg;
 	memcpy(P.cls, hp.cls, 32);
+}
+
+// Parameters of the n-th pass in execution order when it is an upper pass (kind 1).
+inline void plan_fill_upper(const HostPlan& hp, UpperParams& U, int n, const uint32_t* src, uint32_t* dst, const uint32_t* consts,
+                            bool inverse, int coset, bool one_coset = false) {
+	const int np = (int)hp.passes.size();
+	const PassDesc& pd = inverse ? hp.passes[np - 1 - n] : hp.passes[n];
+	memset(&U, 0, sizeof U);
+	const uint64_t row_words = (uint64_t)32 << hp.nb;
+	const bool single = inverse || one_coset;
+	const int rows = single ? hp.batch : hp.batch << hp.log_rate;
+	const bool first_pass = n == 0, last_pass = n == np - 1;
+	U.src = first_pass ? src : dst;
+	U.dst = dst;
+	U.src_row_words = U.dst_row_words = row_words;
+	U.src_row_shift = (first_pass && !single) ? hp.log_rate : 0;
+	U.coset_mask = single ? 0u : ((1u << hp.log_rate) - 1);
+	U.coset0 = single ? coset : 0;
+	U.consts = consts;
+	U.log_h = hp.log_h, U.nb = hp.nb, U.q0 = pd.q0, U.k = pd.k;
+	U.stage0 = hp.n_inline + pd.q0 - hp.batch_bits;
+	U.src_sliced = (hp.sliced_io || !first_pass) ? 1 : 0;
+	U.dst_sliced = (hp.sliced_io || !last_pass) ? 1 : 0;
+	U.inverse = inverse ? 1 : 0;
+	U.n_groups = (uint64_t)rows << (hp.nb - pd.k - 5);
+	for (int i = 0; i < pd.k; i++) U.cls[i] = hp.cls[U.stage0 + i];
 }
 
 // Top phase of a transform split over 2^log_seg devices: the buffer holds

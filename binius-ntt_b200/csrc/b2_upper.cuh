@@ -1,0 +1,282 @@
+// b2_upper.cuh -- "upper" passes of the additive NTT: butterfly layers whose stride is at least
+// 32 lines (4 KB), fused two or four per pass, with WARP-UNIFORM twiddles.
+//
+// Index split of a pass that owns the line bits [q0, q0+k), q0 >= 5, k in {2, 4}:
+//     line = hi << (q0+k) | x << q0 | lo_hi << 5 | t          t = lane of the warp (5 bits)
+// A "super-line" is the 32 consecutive lines (4 KB) of one (hi, x, lo_hi); lane t owns line t of
+// every super-line it meets, held bit-sliced in 32 registers (a bundle, b2_bundle.cuh).  All 32 x
+// 32 words of a super-line meet the same twiddle in every layer of the pass (the twiddle of
+// ntt/additive_ntt.cuh:59-77 depends only on the index bits above the butterfly bit), so:
+//   * the product w * V is a CONSTANT multiplication: everything on the w side of the Karatsuba
+//     circuit (bit masks, the pre-additions) is computed once per (coset row, hi) into a small
+//     shared-memory table of "leaf masks" and fetched by warp-broadcast 16-byte loads, and the
+//     butterfly costs only the V-side network (about 23 % fewer logic operations);
+//   * lanes never exchange data: a warp runs two layers (a radix-4 block over 4 super-lines) on
+//     registers alone, loading its lines straight from global memory.  With k = 4 the 4 warps of a
+//     CTA swap super-lines once through shared memory (one __syncthreads per group); with k = 2
+//     there is no exchange at all and every warp works on its own group.
+//
+// Replaces, for these layers, additive_ntt_kernel (ntt/additive_ntt.cuh:91-160).  The phase
+// functions take the thread identity as arguments so tests/emul can drive them on the CPU.
+#pragma once
+#include "b2_pass.cuh"
+
+namespace b2 {
+
+constexpr int kUpperWarps = 4;        // warps per CTA
+constexpr int kLeafPitch = 81 * 4;    // words per twiddle in the leaf-mask table (class 5: 81 GF(4) groups x {m0, m1, m0^m1, pad})
+constexpr int kUpperMaxTw = 15;       // twiddles of a k = 4 group: 8 + 4 + 2 + 1
+
+struct alignas(16) Mask4 {
+	uint32_t x, y, z, w;
+};
+
+// ---- constant multiplication, V side only ---------------------------------------------------------
+// out = a * w for a lane-uniform w in GF(2^(2^H)) given by its 3^(H-1) leaf groups m[] (ternary order,
+// top level most significant: 0 = low half, 1 = high half, 2 = low ^ high).  a: 2^H words.
+template <int H>
+struct ConstMul {
+	static constexpr int N = 1 << H, M = N / 2;
+	using Sub = ConstMul<H - 1>;
+	static constexpr int G = 3 * Sub::G;
+	static B2_HD void mul(const uint32_t* a, const Mask4* m, uint32_t* out) {
+		uint32_t sa[M], z0[M], z2[M], zz[M], za[M];
+#pragma unroll
+		for (int i = 0; i < M; i++) sa[i] = a[i] ^ a[M + i];
+		Sub::mul(a, m, z0);
+		Sub::mul(a + M, m + Sub::G, z2);
+		Sub::mul(sa, m + 2 * Sub::G, zz);
+		Sliced<H - 1>::mul_alpha(z2, za);
+#pragma unroll
+		for (int i = 0; i < M; i++) {
+			const uint32_t lo = z0[i] ^ z2[i];
+			out[i] = lo;
+			out[M + i] = zz[i] ^ lo ^ za[i];
+		}
+	}
+};
+// GF(4): (a0 + a1 X)(w0 + w1 X), X^2 = X + 1  ->  (a0 w0 + a1 w1) + (a0 w1 + a1 (w0 + w1)) X
+template <>
+struct ConstMul<1> {
+	static constexpr int G = 1;
+	static B2_HD void mul(const uint32_t* a, const Mask4* m, uint32_t* out) {
+		const Mask4 q = m[0];
+		out[0] = (a[0] & q.x) ^ (a[1] & q.y);
+		out[1] = (a[0] & q.y) ^ (a[1] & q.z);
+	}
+};
+
+// leaf group g (ternary digits, top level first) of a twiddle w of class HW: the two bits of the
+// GF(4) value at that node of the w-side Karatsuba tree, as all-ones / all-zeros words
+B2_HD Mask4 leaf_group(uint32_t w, int hw, int g) {
+	int div = 1;
+	for (int l = 1; l < hw - 1; l++) div *= 3;  // 3^(hw-2): weight of the top digit
+	uint32_t v = w;
+	for (int bits = 1 << hw; bits > 2; bits >>= 1) {
+		const int d = g / div;
+		g -= d * div;
+		div /= 3;
+		const int half = bits >> 1;
+		const uint32_t lo = v & ((1u << half) - 1), hi = (v >> half) & ((1u << half) - 1);
+		v = d == 0 ? lo : d == 1 ? hi : lo ^ hi;
+	}
+	Mask4 q;
+	q.x = 0u - (v & 1u), q.y = 0u - ((v >> 1) & 1u), q.z = q.x ^ q.y, q.w = 0;
+	return q;
+}
+B2_HD int leaf_groups(int hw) { return hw == 5 ? 81 : hw == 4 ? 27 : hw == 3 ? 9 : hw == 2 ? 3 : 0; }
+
+// U ^= w * V ; V ^= U  (forward) or  V ^= U ; U ^= w * V  (inverse); w of class HW given by its leaf masks
+template <int HW, bool INV>
+B2_HD void butterfly_const(uint32_t* U, uint32_t* V, const Mask4* m) {
+	if (INV) {
+#pragma unroll
+		for (int i = 0; i < 32; i++) V[i] ^= U[i];
+	}
+	if constexpr (HW > 0) {
+		constexpr int C = 1 << HW;
+#pragma unroll
+		for (int c = 0; c < 32 / C; c++) {
+			uint32_t p[C];
+			ConstMul<HW>::mul(V + c * C, m, p);
+#pragma unroll
+			for (int i = 0; i < C; i++) U[c * C + i] ^= p[i];
+		}
+	}
+	if (!INV) {
+#pragma unroll
+		for (int i = 0; i < 32; i++) V[i] ^= U[i];
+	}
+}
+template <bool INV>
+B2_HD void butterfly_const_dispatch(int cls, uint32_t* U, uint32_t* V, const Mask4* m) {
+	switch (cls) {
+		case 0: butterfly_const<0, INV>(U, V, m); break;
+		case 2: butterfly_const<2, INV>(U, V, m); break;
+		case 3: butterfly_const<3, INV>(U, V, m); break;
+		case 4: butterfly_const<4, INV>(U, V, m); break;
+		default: butterfly_const<5, INV>(U, V, m); break;
+	}
+}
+
+// ---- pass description ---------------------------------------------------------------------------
+struct UpperParams {
+	const uint32_t* src;   // row r reads words [(r >> src_row_shift) * src_row_words, ...)
+	uint32_t* dst;         // row r at r * dst_row_words
+	uint64_t src_row_words, dst_row_words;
+	int src_row_shift;     // log_rate when the first pass fans one column out to its coset rows
+	uint32_t coset_mask;   // row & coset_mask = coset of the row
+	int coset0;            // coset of row 0 (single-coset transforms)
+	const uint32_t* consts;  // [32][kConstPitch] normalised subspace constants (additive_ntt.cuh:273-309)
+	int log_h;             // of the whole transform (twiddle index shift)
+	int nb;                // line bits per row
+	int q0, k;             // this pass owns line bits [q0, q0+k), q0 >= 5, k = 2 or 4
+	int stage0;            // butterfly stage of local bit 0
+	int src_sliced, dst_sliced;  // lines are bundles already / stay bundles (no 32x32 transpose)
+	int inverse;
+	uint64_t n_groups;     // rows << (nb - k - 5)
+	uint8_t cls[4];        // twiddle class of local bit i (0, 2..5)
+};
+
+constexpr int kUSlotWords = 36;  // padded line slot in the exchange buffer (as b2_pass.cuh)
+B2_HD size_t upper_smem_words(int k) {
+	(void)k;
+	return (size_t)kUpperMaxTw * kLeafPitch + 16 + (size_t)16 * 32 * kUSlotWords;
+}
+struct UpperSmem {
+	Mask4* leaves;     // [kUpperMaxTw][81]
+	uint32_t* tw;      // [16] twiddle words
+	uint32_t* slots;   // [16 super-lines][32 lanes][kUSlotWords]; k = 2: 4 super-lines per warp
+};
+B2_HD UpperSmem upper_smem_view(uint32_t* base) {
+	UpperSmem sm;
+	sm.leaves = reinterpret_cast<Mask4*>(base);
+	sm.tw = base + kUpperMaxTw * kLeafPitch;
+	sm.slots = sm.tw + 16;
+	return sm;
+}
+
+struct UGroup {
+	uint32_t row;
+	uint64_t hi, lo_hi;
+};
+B2_HD UGroup upper_group(const UpperParams& P, uint64_t g) {
+	UGroup c;
+	const int gb = P.nb - P.k - 5;  // group bits per row
+	c.row = (uint32_t)(g >> gb);
+	const uint64_t rem = g & ((uint64_t(1) << gb) - 1);
+	c.lo_hi = rem & ((uint64_t(1) << (P.q0 - 5)) - 1);
+	c.hi = rem >> (P.q0 - 5);
+	return c;
+}
+B2_HD uint64_t upper_line(const UpperParams& P, const UGroup& c, int x, int lane) {
+	return (c.hi << (P.q0 + P.k)) | ((uint64_t)x << P.q0) | (c.lo_hi << 5) | (uint64_t)lane;
+}
+// table index of the twiddle of layer i for the super-line x (depends on x >> (i+1))
+B2_HD int upper_tw_index(int k, int i, int x) { return (1 << (k - 1 - i)) - 1 + (x >> (i + 1)); }
+
+// twiddle words of (row, hi): threads tid < 2^k - 1
+B2_HD void upper_twiddles(const UpperParams& P, UpperSmem& sm, const UGroup& c, int tid) {
+	if (tid >= (1 << P.k) - 1) return;
+	int lg = 0;
+	while ((tid + 1) >> (lg + 1)) lg++;
+	const int i = P.k - 1 - lg, j = tid + 1 - (1 << lg);
+	const int stage = P.stage0 + i;
+	const uint64_t ind = ((uint64_t)(P.coset0 + (c.row & P.coset_mask)) << (P.log_h - 1 - stage)) | (c.hi << (P.k - 1 - i)) | (uint64_t)j;
+	uint32_t w = 0;
+	const uint32_t* t = P.consts + stage * 32;
+	for (int b = 0; (ind >> b) != 0; b++)
+		if ((ind >> b) & 1) w ^= t[b];
+	sm.tw[tid] = w;
+}
+// leaf masks of every twiddle: item = twiddle * 81 + group, strided over nthreads
+B2_HD void upper_leaves(const UpperParams& P, UpperSmem& sm, int tid, int nthreads) {
+	const int ntw = (1 << P.k) - 1;
+	for (int item = tid; item < ntw * 81; item += nthreads) {
+		const int tw = item / 81, g = item - tw * 81;
+		int lg = 0;
+		while ((tw + 1) >> (lg + 1)) lg++;
+		const int hw = P.cls[P.k - 1 - lg];
+		if (g < leaf_groups(hw)) sm.leaves[tw * 81 + g] = leaf_group(sm.tw[tw], hw, g);
+	}
+}
+
+// ---- one line (32 words) <-> registers -----------------------------------------------------------
+B2_HD void line_load(const uint32_t* p, uint32_t* w) {
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+	for (int g = 0; g < 8; g++) {
+		const uint4 v = reinterpret_cast<const uint4*>(p)[g];
+		w[4 * g] = v.x, w[4 * g + 1] = v.y, w[4 * g + 2] = v.z, w[4 * g + 3] = v.w;
+	}
+#else
+	for (int j = 0; j < 32; j++) w[j] = p[j];
+#endif
+}
+B2_HD void line_store(uint32_t* p, const uint32_t* w) {
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+	for (int g = 0; g < 8; g++) reinterpret_cast<uint4*>(p)[g] = make_uint4(w[4 * g], w[4 * g + 1], w[4 * g + 2], w[4 * g + 3]);
+#else
+	for (int j = 0; j < 32; j++) p[j] = w[j];
+#endif
+}
+
+// Two butterfly layers (local bits b1 and b1 - 1) of one lane over the 4 super-lines x(a) = xbase | a << xshift,
+// a = a1 a0, held in the slots slot_off + x(a).  The lane's lines are private to it, so the two layers need
+// no synchronisation.  The loops are deliberately NOT unrolled: one copy of each butterfly circuit serves
+// all 4 butterflies, which keeps the executed code inside the instruction cache.
+//   first: the slots hold lines as copied from the pass input (transpose compact lines on first touch)
+//   last : the slots are copied to the pass output afterwards (transpose back for a compact output)
+template <bool INV>
+B2_HD void upper_pair(const UpperParams& P, const UpperSmem& sm, int lane, int xbase, int xshift, int slot_off, int b1, bool first, bool last) {
+	const int k = P.k;
+#pragma unroll 1
+	for (int step = 0; step < 2; step++) {
+		const bool top = INV ? step == 1 : step == 0;  // which of the two layers
+		const int bit = top ? b1 : b1 - 1;
+		const int cls = P.cls[bit];
+#pragma unroll 1
+		for (int j = 0; j < 2; j++) {
+			const int au = top ? j : 2 * j, av = top ? j + 2 : 2 * j + 1;
+			const int xu = xbase | (au << xshift), xv = xbase | (av << xshift);
+			uint32_t* su = sm.slots + ((size_t)(slot_off + xu) * 32 + lane) * kUSlotWords;
+			uint32_t* sv = sm.slots + ((size_t)(slot_off + xv) * 32 + lane) * kUSlotWords;
+			uint32_t U[32], V[32];
+			line_load(su, U);
+			line_load(sv, V);
+			if (first && step == 0 && !P.src_sliced) {
+				transpose32(U);
+				transpose32(V);
+			}
+			butterfly_const_dispatch<INV>(cls, U, V, sm.leaves + 81 * upper_tw_index(k, bit, xu));
+			if (last && step == 1 && !P.dst_sliced) {
+				transpose32(U);
+				transpose32(V);
+			}
+			line_store(su, U);
+			line_store(sv, V);
+		}
+	}
+}
+
+// ---- coalesced copies of super-lines: global <-> slots, 16-byte chunks ---------------------------------
+// chunk ch of a set of `nsl` super-lines: piece = ch & 7, line = (ch >> 3) & 31, super-line = ch >> 8
+template <bool STORE>
+B2_HD void upper_copy(const UpperParams& P, const UpperSmem& sm, const UGroup& c, int slot_off, int nsl, int tid, int nthreads) {
+	const uint32_t* srow = P.src + (uint64_t)(c.row >> P.src_row_shift) * P.src_row_words;
+	uint32_t* drow = P.dst + (uint64_t)c.row * P.dst_row_words;
+#pragma unroll 4
+	for (int ch = tid; ch < nsl * 256; ch += nthreads) {
+		const int piece = ch & 7, ln = (ch >> 3) & 31, x = ch >> 8;
+		uint32_t* s = sm.slots + ((size_t)(slot_off + x) * 32 + ln) * kUSlotWords + piece * 4;
+		const uint64_t off = upper_line(P, c, x, ln) * 32 + piece * 4;
+		if (STORE)
+			copy16_s2g(drow + off, s);
+		else
+			copy16_g2s(s, srow + off);
+	}
+	if (!STORE) copy_wait_all();
+}
+
+}  // namespace b2

@@ -55,7 +55,9 @@ extern "C" int b2ntt_plan_create(b2ntt_plan** out, int field_bits, int layout, i
 	if (const char* e = getenv("B2NTT_CTA_THREADS")) cta = atoi(e);  // tuning knob: 64, 128 or 256
 	int glines = 0;
 	if (const char* e = getenv("B2NTT_GROUP_LINES")) glines = atoi(e);  // tuning knob: 128, 256 or 512
-	if (plan_build(p->hp, field_bits, layout, log_h, log_rate, batch, cta, glines)) {
+	int upper = 1;
+	if (const char* e = getenv("B2NTT_UPPER")) upper = atoi(e);  // tuning knob: 0 = bundle passes only
+	if (plan_build(p->hp, field_bits, layout, log_h, log_rate, batch, cta, glines, upper)) {
 		delete p;
 		return B2NTT_EINVAL;
 	}
@@ -115,8 +117,14 @@ static int run(b2ntt_plan* p, const void* d_in, void* d_out, bool inverse, int c
 		return B2NTT_OK;
 	}
 	PassParams P;
+	UpperParams U;
 	const int np = (int)hp.passes.size();
 	for (int n = 0; n < np; n++) {
+		if ((inverse ? hp.passes[np - 1 - n] : hp.passes[n]).kind == 1) {
+			plan_fill_upper(hp, U, n, src, dst, p->d_consts, inverse, coset, one_coset);
+			if (launch_upper(U, st)) return cuda_fail(cudaGetLastError(), "launch_upper");
+			continue;
+		}
 		plan_fill_pass(hp, P, n, src, dst, p->d_consts, p->d_lane_tw, inverse, coset, one_coset);
 		if (launch_pass(P, st)) return cuda_fail(cudaGetLastError(), "launch_pass");
 	}

@@ -29,14 +29,50 @@ static void run_pass(const PassParams& P) {
 	}
 }
 
+// upper passes (b2_upper.cuh): same phase functions as upper_kernel, CTA of 4 warps, one group at a time
+template <bool INV>
+static void run_upper(const UpperParams& P) {
+	std::vector<uint32_t> mem(upper_smem_words(4) + 8);
+	UpperSmem sm = upper_smem_view(mem.data());
+	const int T = kUpperWarps * 32;
+	for (uint64_t grp = 0; grp < P.n_groups; grp++) {
+		const UGroup c = upper_group(P, grp);
+		for (int t = 0; t < T; t++) upper_twiddles(P, sm, c, t);
+		for (int t = 0; t < T; t++) upper_leaves(P, sm, t, T);
+		if (P.k == 4) {
+			for (int t = 0; t < T; t++) upper_copy<false>(P, sm, c, 0, 16, t, T);
+			for (int t = 0; t < T; t++) {
+				if (!INV) upper_pair<INV>(P, sm, t & 31, t >> 5, 2, 0, 3, true, false);
+				else upper_pair<INV>(P, sm, t & 31, (t >> 5) << 2, 0, 0, 1, true, false);
+			}
+			for (int t = 0; t < T; t++) {
+				if (!INV) upper_pair<INV>(P, sm, t & 31, (t >> 5) << 2, 0, 0, 1, false, true);
+				else upper_pair<INV>(P, sm, t & 31, t >> 5, 2, 0, 3, false, true);
+			}
+			for (int t = 0; t < T; t++) upper_copy<true>(P, sm, c, 0, 16, t, T);
+		} else {
+			const int w = (int)(grp & 3);  // any warp slot
+			for (int t = 0; t < 32; t++) upper_copy<false>(P, sm, c, w * 4, 4, t, 32);
+			for (int t = 0; t < 32; t++) upper_pair<INV>(P, sm, t, 0, 0, w * 4, 1, true, true);
+			for (int t = 0; t < 32; t++) upper_copy<true>(P, sm, c, w * 4, 4, t, 32);
+		}
+	}
+}
+
 extern "C" int emul_antt_cta(int field_bits, int layout, int log_h, int log_rate, int batch, const uint32_t* in,
                              uint32_t* out, int inverse, int coset, int cta_threads, int group_lines) {
 	HostPlan hp;
 	if (plan_build(hp, field_bits, layout, log_h, log_rate, batch, cta_threads, group_lines)) return -1;
 	if (hp.tiny) return -4;
 	PassParams P;
+	UpperParams U;
 	const int np = (int)hp.passes.size();
 	for (int n = 0; n < np; n++) {
+		if ((inverse ? hp.passes[np - 1 - n] : hp.passes[n]).kind == 1) {
+			plan_fill_upper(hp, U, n, in, out, hp.consts, inverse != 0, coset);
+			if (inverse) run_upper<true>(U); else run_upper<false>(U);
+			continue;
+		}
 		plan_fill_pass(hp, P, n, in, out, hp.consts, hp.lane_tw, inverse != 0, coset);
 		if (inverse) run_pass<true>(P); else run_pass<false>(P);
 	}

@@ -52,4 +52,7 @@ def logic_peak(iters=200, lop3_per_mul=990):
 
 
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) >= 3:  # quick_time.py FIELD LOG_H [ITERS]: one shape (for ncu launch lists)
+        time_plan(int(sys.argv[1]), int(sys.argv[2]), iters=int(sys.argv[3]) if len(sys.argv) > 3 else 2)
+    else:
+        main()
