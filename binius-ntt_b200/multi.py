@@ -95,7 +95,7 @@ class FourStepNTT:
         self.device = device
         self._make_plans()
 
-    # -- the two local phases: libb2ntt.so only (overridden by the CPU tests with the oracle) ----------
+    # -- the two local phases: libb2ntt.so only (the CPU tests override them) ----------------------
     def _make_plans(self):
         dev = torch.cuda.current_device() if self.device is None else self.device
         self.device = dev
