@@ -38,6 +38,7 @@ def lib():
         L.b2ntt_exec.argtypes = [vp, vp, vp, vp]
         L.b2ntt_exec_inverse.argtypes = [vp, vp, vp, i, vp]
         L.b2ntt_exec_host.argtypes = [vp, vp, sz, vp]
+        L.b2ntt_exec_profile.argtypes = [vp, vp, vp, vp, vp, vp, i]
         L.b2ntt_exec_coset.argtypes = [vp, vp, vp, i, vp]
         L.b2ntt_exec_top.argtypes = [vp, vp, i, vp]
         L.b2ntt_plan_launches.argtypes = [vp]
@@ -122,6 +123,18 @@ class Plan:
         self._dev_ok(d_out, self.out_words, "d_out")
         _check(lib().b2ntt_exec(self._h, d_in.data_ptr(), d_out.data_ptr(), _stream_ptr(stream)), "b2ntt_exec")
         return d_out
+
+    def exec_profile(self, d_in, d_out=None, stream=None):
+        """exec with per-pass device times: returns [(kernel name, ms), ...] (synchronises)."""
+        self._dev_ok(d_in, self.in_words, "d_in")
+        if d_out is None:
+            d_out = d_in
+        self._dev_ok(d_out, self.out_words, "d_out")
+        ms = (C.c_float * 16)()
+        kind = (C.c_int * 16)()
+        n = lib().b2ntt_exec_profile(self._h, d_in.data_ptr(), d_out.data_ptr(), _stream_ptr(stream), ms, kind, 16)
+        _check(min(n, 0), "b2ntt_exec_profile")
+        return [(("b2::pass_kernel", "b2::upper_kernel", "b2::bottom_kernel")[kind[i]], float(ms[i])) for i in range(n)]
 
     def exec_inverse(self, d_in, d_out=None, coset=0, stream=None):
         self._dev_ok(d_in, self.in_words, "d_in")

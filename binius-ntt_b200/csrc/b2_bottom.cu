@@ -1,0 +1,76 @@
+// b2_bottom.cu -- __global__ wrapper of the lowest pass (b2_bottom.cuh): a 512-line tile per CTA, phase A
+// (strides >= 32 lines, warp-uniform twiddles) and phase B (strides < 32 lines and the layers inside a
+// line, warp-local).  sm_100a only.  Replaces additive_ntt_kernel<T,P> (ntt/additive_ntt.cuh:91-160).
+#include <cuda_runtime.h>
+
+#include "b2_bottom.cuh"
+#include "b2_launch.h"
+
+namespace b2 {
+
+template <bool INV>
+__global__ void __launch_bounds__(kUpperWarps * 32, 2) bottom_kernel(const __grid_constant__ BottomParams B) {
+	extern __shared__ __align__(16) uint32_t bsmem_raw[];
+	BottomSmem bs = bottom_smem_view(bsmem_raw);
+	const UpperParams& P = B.up;
+	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, T = kUpperWarps * 32;
+	const int nline = 5 - B.batch_bits;
+	for (int i = tid; i < 1024; i += T) bs.us.consts[i] = P.consts[i];
+	__syncthreads();
+	bottom_prologue(B, bs, tid, T, bs.us.consts);
+	const uint64_t per = (P.n_groups + gridDim.x - 1) / gridDim.x;
+	const uint64_t g0 = per * blockIdx.x, g1 = g0 + per < P.n_groups ? g0 + per : P.n_groups;
+#pragma unroll 1
+	for (uint64_t grp = g0; grp < g1; grp++) {
+		const UGroup c = upper_group(P, grp);  // hi = tile index of the row
+		upper_copy<false>(P, bs.us, c, 0, 16, tid, T);  // cp.async in flight while the tables are built
+		upper_twiddles(P, bs.us, c, tid, bs.us.consts);
+		bottom_tile_tables(B, bs, c, tid - 16, bs.us.consts);
+		__syncthreads();
+		upper_leaves(P, bs.us, tid, T);
+		copy_wait_all();
+		__syncthreads();
+		if (!INV) {
+			upper_pair<false>(P, bs.us, lane, warp, 2, 0, 3, true, false);
+			__syncthreads();
+			upper_pair<false>(P, bs.us, lane, warp << 2, 0, 0, 1, false, false);
+			__syncwarp();
+		}
+#pragma unroll 1
+		for (int iter = 0; iter < 2; iter++) {
+#pragma unroll 1
+			for (int n = 0; n < nline; n++) {
+				bottom_phase_b<INV>(B, bs, warp, lane, iter, n);
+				__syncwarp();
+			}
+		}
+		if (INV) {
+			upper_pair<true>(P, bs.us, lane, warp << 2, 0, 0, 1, false, false);
+			__syncthreads();
+			upper_pair<true>(P, bs.us, lane, warp, 2, 0, 3, false, true);
+		}
+		__syncthreads();
+		upper_copy<true>(P, bs.us, c, 0, 16, tid, T);
+		__syncthreads();
+	}
+}
+
+template <bool INV>
+static int launch_bottom_t(const BottomParams& B, cudaStream_t stream) {
+	int sms = 0, dev = 0;
+	const size_t smem = bottom_smem_words() * sizeof(uint32_t);
+	cudaGetDevice(&dev);
+	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+	cudaFuncSetAttribute(bottom_kernel<INV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+	uint64_t ctas = (uint64_t)sms * 2 * 4;
+	if (ctas > B.up.n_groups) ctas = B.up.n_groups;
+	if (ctas == 0) return -1;
+	bottom_kernel<INV><<<(unsigned)ctas, kUpperWarps * 32, smem, stream>>>(B);
+	return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
+int launch_bottom(const BottomParams& B, cudaStream_t stream) {
+	return B.up.inverse ? launch_bottom_t<true>(B, stream) : launch_bottom_t<false>(B, stream);
+}
+
+}  // namespace b2

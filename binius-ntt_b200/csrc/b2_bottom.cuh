@@ -1,0 +1,135 @@
+// b2_bottom.cuh -- the lowest pass of the additive NTT: a tile of 512 consecutive lines (64 KB) per CTA.
+//
+//   line bits 5..8 of the tile ("phase A") -- strides of 32..256 lines: exactly an upper pass with q0 = 5
+//       (b2_upper.cuh): warp-uniform twiddles, leaf-mask constant multiply, lane-private lines, one
+//       __syncthreads between its two layer pairs;
+//   line bits bb..4 ("phase B", bb = batch_bits) -- pairs of lines inside one super-line, and the
+//       butterfly layers INSIDE a line: per-lane twiddles, bit-sliced Karatsuba product.  After phase A
+//       warp w owns the super-lines 4w..4w+3, so phase B needs only __syncwarp between its layers.
+//
+// Replaces additive_ntt_kernel (ntt/additive_ntt.cuh:91-160) for the stages below 2^(9-bb) lines and the
+// 32x32 bit transposes between the compact image and the bundle form.
+#pragma once
+#include "b2_upper.cuh"
+
+namespace b2 {
+
+struct BottomParams {
+	UpperParams up;          // phase A: k = 4, q0 = 5 (n_groups = tiles)
+	const uint32_t* lane_tw; // [5][32] per-lane twiddle words of the in-line layers
+	int n_inline;            // butterfly layers inside a line
+	int lane_shift;          // in-line layer s pairs lanes differing in bit s + lane_shift
+	int batch_bits;          // low line bits that are not butterfly bits
+	uint8_t cls[32];         // twiddle class per stage
+};
+
+// shared-memory image after the upper part: [TL 512][TH 8][IH 8][IL 5*512][lane_tw 160]
+struct BottomSmem {
+	UpperSmem us;
+	uint32_t* TL;   // line-layer twiddle, tile-independent part: heap order, bit b owns [2^(8-b), 2^(9-b)) - index (1 << (8-b)) + (l >> (b+1))
+	uint32_t* TH;   // [8] line-layer twiddle, per tile and coset: by line bit
+	uint32_t* IH;   // [8] in-line twiddle, per tile and coset: by stage
+	uint32_t* IL;   // [n_inline][512] in-line twiddle by local line
+	uint32_t* LT;   // [5][32] lane_tw copy
+};
+B2_HD size_t bottom_smem_words() { return upper_smem_words(4) + 512 + 8 + 8 + 5 * 512 + 160; }
+B2_HD BottomSmem bottom_smem_view(uint32_t* base) {
+	BottomSmem b;
+	b.us = upper_smem_view(base);
+	b.TL = base + upper_smem_words(4);
+	b.TH = b.TL + 512;
+	b.IH = b.TH + 8;
+	b.IL = b.IH + 8;
+	b.LT = b.IL + 5 * 512;
+	return b;
+}
+
+B2_HD uint32_t xsel(const uint32_t* table, uint64_t bits) {
+	uint32_t w = 0;
+	for (int b = 0; bits; b++, bits >>= 1)
+		if (bits & 1u) w ^= table[b];
+	return w;
+}
+B2_HD int bottom_stage(const BottomParams& B, int bit) { return B.n_inline + bit - B.batch_bits; }
+
+// once per CTA: tile-independent tables
+B2_HD void bottom_prologue(const BottomParams& B, BottomSmem& bs, int tid, int nthreads, const uint32_t* consts) {
+	for (int i = tid; i < 160; i += nthreads) bs.LT[i] = B.lane_tw[i];
+	for (int idx = tid; idx < 512; idx += nthreads) {
+		if (idx == 0) {
+			bs.TL[0] = 0;
+			continue;
+		}
+		int lg = 0;
+		while (idx >> (lg + 1)) lg++;
+		const int bit = 8 - lg;  // bit b owns [2^(8-b), 2^(9-b))
+		bs.TL[idx] = bit >= B.batch_bits ? xsel(consts + bottom_stage(B, bit) * 32, (uint64_t)(idx - (1 << lg))) : 0u;
+	}
+	// in-line stage s, local line l: block index (butterfly-line part of l) << (n_inline-1-s)
+	for (int idx = tid; idx < B.n_inline * 512; idx += nthreads) {
+		const int s = idx >> 9, l = idx & 511;
+		bs.IL[idx] = xsel(consts + s * 32, (uint64_t)(l >> B.batch_bits) << (B.n_inline - 1 - s));
+	}
+}
+// once per tile: the tile- and coset-dependent parts (threads 0..15)
+B2_HD void bottom_tile_tables(const BottomParams& B, BottomSmem& bs, const UGroup& c, int tid, const uint32_t* consts) {
+	const UpperParams& P = B.up;
+	const uint64_t coset = (uint64_t)(P.coset0 + (c.row & P.coset_mask));
+	if (tid < 0) return;
+	if (tid < 8) {  // line bit tid (only batch_bits..4 are used here; 5..8 go through the leaf masks)
+		const int bit = tid;
+		if (bit >= B.batch_bits && bit < 5) {
+			const int stage = bottom_stage(B, bit);
+			bs.TH[bit] = xsel(consts + stage * 32, (coset << (P.log_h - 1 - stage)) | (c.hi << (8 - bit)));
+		}
+	} else if (tid < 16) {
+		const int s = tid - 8;
+		if (s < B.n_inline) bs.IH[s] = xsel(consts + s * 32, (coset << (P.log_h - 1 - s)) | (c.hi << (9 - B.batch_bits + B.n_inline - 1 - s)));
+	}
+}
+
+// Phase B for one lane: the warp's super-lines 4*warp .. 4*warp+3, two at a time (iter; 16 lanes x 2 lines each).
+// n-th line layer in execution order, n < 5 - batch_bits; callers put __syncwarp() between layers.  The in-line
+// layers and the transposes ride on the layer that touches a line last (forward) or first (inverse).
+template <bool INV>
+B2_HD void bottom_phase_b(const BottomParams& B, const BottomSmem& bs, int warp, int lane, int iter, int n) {
+	const UpperParams& P = B.up;
+	const int bb = B.batch_bits, L0 = B.n_inline;
+	const int sl = 4 * warp + 2 * iter + (lane >> 4), tt = lane & 15;
+	uint32_t* slot0 = bs.us.slots + (size_t)sl * 32 * kUSlotWords;
+	const int nline = 5 - bb;
+	uint32_t U[32], V[32];
+	{
+		const int b = INV ? bb + n : 4 - n;  // forward: 4 .. bb, inverse: bb .. 4
+		const int lu = ((tt >> b) << (b + 1)) | (tt & ((1 << b) - 1)), lv = lu | (1 << b);
+		uint32_t* su = slot0 + (size_t)lu * kUSlotWords;
+		uint32_t* sv = slot0 + (size_t)lv * kUSlotWords;
+		line_load(su, U);
+		line_load(sv, V);
+		const int l_u = (sl << 5) | lu, l_v = (sl << 5) | lv;
+		if (INV && n == 0) {  // first touch: back from the compact image, then the in-line layers upwards
+			if (!P.src_sliced) {
+				transpose32(U);
+				transpose32(V);
+			}
+#pragma unroll 1
+			for (int s = 0; s < L0; s++)
+				in_line_dispatch<true>(B.cls[s], U, V, s + B.lane_shift, bs.LT + s * 32, bs.IH[s] ^ bs.IL[s * 512 + l_u], bs.IH[s] ^ bs.IL[s * 512 + l_v]);
+		}
+		const uint32_t w = bs.TH[b] ^ bs.TL[(1 << (8 - b)) + (l_u >> (b + 1))];
+		uniform_dispatch<INV>(B.cls[bottom_stage(B, b)], U, V, w);
+		if (!INV && n == nline - 1) {  // last touch: the in-line layers downwards, then the compact image
+#pragma unroll 1
+			for (int s = L0 - 1; s >= 0; s--)
+				in_line_dispatch<false>(B.cls[s], U, V, s + B.lane_shift, bs.LT + s * 32, bs.IH[s] ^ bs.IL[s * 512 + l_u], bs.IH[s] ^ bs.IL[s * 512 + l_v]);
+			if (!P.dst_sliced) {
+				transpose32(U);
+				transpose32(V);
+			}
+		}
+		line_store(su, U);
+		line_store(sv, V);
+	}
+}
+
+}  // namespace b2

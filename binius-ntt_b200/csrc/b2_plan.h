@@ -12,7 +12,7 @@
 #include <vector>
 
 #include "b2_pass.cuh"
-#include "b2_upper.cuh"
+#include "b2_bottom.cuh"
 
 namespace b2 {
 
@@ -20,7 +20,8 @@ struct PassDesc {
 	int q0;       // first line bit
 	int k;        // line bits fused
 	int in_line;  // run the in-line layers in this pass
-	int kind;     // 0: bundle pass through shared memory (b2_pass.cuh), 1: upper pass with warp-uniform twiddles (b2_upper.cuh)
+	int kind;     // 0: bundle pass through shared memory (b2_pass.cuh), 1: upper pass with warp-uniform twiddles (b2_upper.cuh),
+	              // 2: lowest pass on 512-line tiles (b2_bottom.cuh)
 };
 
 struct HostPlan {
@@ -77,7 +78,7 @@ inline int twiddle_class(uint32_t or_of_values) {
 }
 
 inline int plan_build(HostPlan& hp, int field_bits, int layout, int log_h, int log_rate, int batch, int cta_threads = 0, int group_lines = 0,
-                      int use_upper = 1) {
+                      int use_upper = 2) {
 	if (!plan_args_ok(field_bits, layout, log_h, log_rate, batch)) return -1;
 	hp.field_bits = field_bits, hp.layout = layout, hp.log_h = log_h, hp.log_rate = log_rate, hp.batch = batch;
 	hp.limbs_log = field_bits == 128 ? 2 : 0;
@@ -112,7 +113,26 @@ inline int plan_build(HostPlan& hp, int field_bits, int layout, int log_h, int l
 	const int nbf = hp.nb - hp.batch_bits;  // butterfly line bits
 	hp.passes.clear();
 	hp.tiny = nbf < 1;
-	if (!hp.tiny && use_upper && nbf > max_bits && max_bits >= 6) {
+	if (!hp.tiny && use_upper == 2 && nbf >= 9 - hp.batch_bits) {
+		// lowest pass: 512-line tiles (kind 2) = 9 - batch_bits butterfly line bits; above it upper passes of 4
+		// (or 2) line bits; an odd remainder goes to one bundle pass of 3 (or 1) bits at the top
+		const int kb = 9 - hp.batch_bits;
+		int left = nbf - kb, q = hp.batch_bits + nbf;
+		if (left & 1) {
+			const int kt = left >= 3 ? 3 : 1;
+			q -= kt, left -= kt;
+			hp.passes.push_back(PassDesc{q, kt, 0, 0});
+		}
+		if (left & 3) {
+			q -= 2, left -= 2;
+			hp.passes.push_back(PassDesc{q, 2, 0, 1});
+		}
+		while (left > 0) {
+			q -= 4, left -= 4;
+			hp.passes.push_back(PassDesc{q, 4, 0, 1});
+		}
+		hp.passes.push_back(PassDesc{hp.batch_bits, kb, 1, 2});
+	} else if (!hp.tiny && use_upper && nbf > max_bits && max_bits >= 6) {
 		// lowest pass: the bundle pass with the in-line layers (8 or 9 line bits); everything above it
 		// has strides >= 32 lines and runs as upper passes of 4 (or 2) line bits, highest first
 		int kb = max_bits;
@@ -208,6 +228,23 @@ inline void plan_fill_upper(const HostPlan& hp, UpperParams& U, int n, const uin
 	U.inverse = inverse ? 1 : 0;
 	U.n_groups = (uint64_t)rows << (hp.nb - pd.k - 5);
 	for (int i = 0; i < pd.k; i++) U.cls[i] = hp.cls[U.stage0 + i];
+}
+
+// Parameters of the lowest pass (kind 2).
+inline void plan_fill_bottom(const HostPlan& hp, BottomParams& B, int n, const uint32_t* src, uint32_t* dst, const uint32_t* consts,
+                             const uint32_t* lane_tw, bool inverse, int coset, bool one_coset = false) {
+	memset(&B, 0, sizeof B);
+	plan_fill_upper(hp, B.up, n, src, dst, consts, inverse, coset, one_coset);
+	UpperParams& U = B.up;
+	U.q0 = 5, U.k = 4;
+	U.stage0 = hp.n_inline + 5 - hp.batch_bits;
+	const bool single = inverse || one_coset;
+	const int rows = single ? hp.batch : hp.batch << hp.log_rate;
+	U.n_groups = (uint64_t)rows << (hp.nb - 9);
+	for (int i = 0; i < 4; i++) U.cls[i] = hp.cls[U.stage0 + i];
+	B.lane_tw = lane_tw;
+	B.n_inline = hp.n_inline, B.lane_shift = hp.lane_shift, B.batch_bits = hp.batch_bits;
+	memcpy(B.cls, hp.cls, 32);
 }
 
 // Top phase of a transform split over 2^log_seg devices: the buffer holds

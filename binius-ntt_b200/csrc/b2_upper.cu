@@ -32,18 +32,21 @@ __global__ void __launch_bounds__(kUpperWarps * 32, 2) upper_kernel(const __grid
 		else
 			__syncwarp();
 	};
+	for (int i = threadIdx.x; i < 1024; i += kUpperWarps * 32) sm.consts[i] = P.consts[i];
+	__syncthreads();
 	uint64_t key = ~uint64_t(0);
 #pragma unroll 1
 	for (uint64_t grp = g0; grp < g1; grp++) {
 		const UGroup c = upper_group(P, grp);
+		upper_copy<false>(P, sm, c, slot_off, nsl, wt, wn);  // cp.async in flight while the tables are built
 		const uint64_t nk = ((uint64_t)c.row << 40) ^ c.hi;
 		if (nk != key) {  // uniform over the worker
 			key = nk;
-			upper_twiddles(P, sm, c, wt);
+			upper_twiddles(P, sm, c, wt, sm.consts);
 			sync();
 			upper_leaves(P, sm, wt, wn);
 		}
-		upper_copy<false>(P, sm, c, slot_off, nsl, wt, wn);
+		copy_wait_all();
 		sync();
 		// k = 4, forward: bits (3,2) on the quads x = a << 2 | warp, then bits (1,0) on x = warp << 2 | a; inverse: the reverse.
 		// k = 2: bits (1,0) on the warp's own 4 super-lines.

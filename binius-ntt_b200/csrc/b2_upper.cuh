@@ -69,14 +69,12 @@ struct ConstMul<1> {
 // leaf group g (ternary digits, top level first) of a twiddle w of class HW: the two bits of the
 // GF(4) value at that node of the w-side Karatsuba tree, as all-ones / all-zeros words
 B2_HD Mask4 leaf_group(uint32_t w, int hw, int g) {
-	int div = 1;
-	for (int l = 1; l < hw - 1; l++) div *= 3;  // 3^(hw-2): weight of the top digit
 	uint32_t v = w;
-	for (int bits = 1 << hw; bits > 2; bits >>= 1) {
-		const int d = g / div;
+	int div = hw == 5 ? 27 : hw == 4 ? 9 : hw == 3 ? 3 : 1;  // 3^(hw-2): weight of the top digit
+	for (int half = 1 << (hw - 1); half > 1; half >>= 1) {
+		const int d = (g >= div) + (g >= 2 * div);  // no integer division on the device
 		g -= d * div;
-		div /= 3;
-		const int half = bits >> 1;
+		div = div == 27 ? 9 : div == 9 ? 3 : 1;
 		const uint32_t lo = v & ((1u << half) - 1), hi = (v >> half) & ((1u << half) - 1);
 		v = d == 0 ? lo : d == 1 ? hi : lo ^ hi;
 	}
@@ -141,18 +139,20 @@ struct UpperParams {
 constexpr int kUSlotWords = 36;  // padded line slot in the exchange buffer (as b2_pass.cuh)
 B2_HD size_t upper_smem_words(int k) {
 	(void)k;
-	return (size_t)kUpperMaxTw * kLeafPitch + 16 + (size_t)16 * 32 * kUSlotWords;
+	return (size_t)kUpperMaxTw * kLeafPitch + 16 + 1024 + (size_t)16 * 32 * kUSlotWords;
 }
 struct UpperSmem {
 	Mask4* leaves;     // [kUpperMaxTw][81]
 	uint32_t* tw;      // [16] twiddle words
+	uint32_t* consts;  // [32][32] copy of the subspace constants
 	uint32_t* slots;   // [16 super-lines][32 lanes][kUSlotWords]; k = 2: 4 super-lines per warp
 };
 B2_HD UpperSmem upper_smem_view(uint32_t* base) {
 	UpperSmem sm;
 	sm.leaves = reinterpret_cast<Mask4*>(base);
 	sm.tw = base + kUpperMaxTw * kLeafPitch;
-	sm.slots = sm.tw + 16;
+	sm.consts = sm.tw + 16;
+	sm.slots = sm.consts + 1024;
 	return sm;
 }
 
@@ -175,8 +175,8 @@ B2_HD uint64_t upper_line(const UpperParams& P, const UGroup& c, int x, int lane
 // table index of the twiddle of layer i for the super-line x (depends on x >> (i+1))
 B2_HD int upper_tw_index(int k, int i, int x) { return (1 << (k - 1 - i)) - 1 + (x >> (i + 1)); }
 
-// twiddle words of (row, hi): threads tid < 2^k - 1
-B2_HD void upper_twiddles(const UpperParams& P, UpperSmem& sm, const UGroup& c, int tid) {
+// twiddle words of (row, hi): threads tid < 2^k - 1; consts = the [32][32] constants (a shared-memory copy on the GPU)
+B2_HD void upper_twiddles(const UpperParams& P, UpperSmem& sm, const UGroup& c, int tid, const uint32_t* consts) {
 	if (tid >= (1 << P.k) - 1) return;
 	int lg = 0;
 	while ((tid + 1) >> (lg + 1)) lg++;
@@ -184,7 +184,7 @@ B2_HD void upper_twiddles(const UpperParams& P, UpperSmem& sm, const UGroup& c, 
 	const int stage = P.stage0 + i;
 	const uint64_t ind = ((uint64_t)(P.coset0 + (c.row & P.coset_mask)) << (P.log_h - 1 - stage)) | (c.hi << (P.k - 1 - i)) | (uint64_t)j;
 	uint32_t w = 0;
-	const uint32_t* t = P.consts + stage * 32;
+	const uint32_t* t = consts + stage * 32;
 	for (int b = 0; (ind >> b) != 0; b++)
 		if ((ind >> b) & 1) w ^= t[b];
 	sm.tw[tid] = w;
@@ -193,7 +193,7 @@ B2_HD void upper_twiddles(const UpperParams& P, UpperSmem& sm, const UGroup& c, 
 B2_HD void upper_leaves(const UpperParams& P, UpperSmem& sm, int tid, int nthreads) {
 	const int ntw = (1 << P.k) - 1;
 	for (int item = tid; item < ntw * 81; item += nthreads) {
-		const int tw = item / 81, g = item - tw * 81;
+		const int tw = (item * 1619) >> 17, g = item - tw * 81;  // item / 81 for item < 1300
 		int lg = 0;
 		while ((tw + 1) >> (lg + 1)) lg++;
 		const int hw = P.cls[P.k - 1 - lg];
@@ -276,7 +276,6 @@ B2_HD void upper_copy(const UpperParams& P, const UpperSmem& sm, const UGroup& c
 		else
 			copy16_g2s(s, srow + off);
 	}
-	if (!STORE) copy_wait_all();
 }
 
 }  // namespace b2

@@ -55,8 +55,8 @@ extern "C" int b2ntt_plan_create(b2ntt_plan** out, int field_bits, int layout, i
 	if (const char* e = getenv("B2NTT_CTA_THREADS")) cta = atoi(e);  // tuning knob: 64, 128 or 256
 	int glines = 0;
 	if (const char* e = getenv("B2NTT_GROUP_LINES")) glines = atoi(e);  // tuning knob: 128, 256 or 512
-	int upper = 1;
-	if (const char* e = getenv("B2NTT_UPPER")) upper = atoi(e);  // tuning knob: 0 = bundle passes only
+	int upper = 2;
+	if (const char* e = getenv("B2NTT_UPPER")) upper = atoi(e);  // tuning knob: 0 = bundle passes only, 1 = upper passes over a bundle pass, 2 = upper passes over the tile pass
 	if (plan_build(p->hp, field_bits, layout, log_h, log_rate, batch, cta, glines, upper)) {
 		delete p;
 		return B2NTT_EINVAL;
@@ -88,7 +88,8 @@ extern "C" int b2ntt_plan_destroy(b2ntt_plan* p) {
 	return B2NTT_OK;
 }
 
-static int run(b2ntt_plan* p, const void* d_in, void* d_out, bool inverse, int coset, cudaStream_t st, bool one_coset = false) {
+static int run(b2ntt_plan* p, const void* d_in, void* d_out, bool inverse, int coset, cudaStream_t st, bool one_coset = false,
+               cudaEvent_t* ev = nullptr /* np + 1 events recorded around the pass launches */) {
 	const HostPlan& hp = p->hp;
 	if (!d_in || !d_out) return B2NTT_EINVAL;
 	const bool single = inverse || one_coset;
@@ -118,15 +119,22 @@ static int run(b2ntt_plan* p, const void* d_in, void* d_out, bool inverse, int c
 	}
 	PassParams P;
 	UpperParams U;
+	BottomParams B;
 	const int np = (int)hp.passes.size();
+	if (ev) CU(cudaEventRecord(ev[0], st));
 	for (int n = 0; n < np; n++) {
-		if ((inverse ? hp.passes[np - 1 - n] : hp.passes[n]).kind == 1) {
+		const int kind = (inverse ? hp.passes[np - 1 - n] : hp.passes[n]).kind;
+		if (kind == 1) {
 			plan_fill_upper(hp, U, n, src, dst, p->d_consts, inverse, coset, one_coset);
 			if (launch_upper(U, st)) return cuda_fail(cudaGetLastError(), "launch_upper");
-			continue;
+		} else if (kind == 2) {
+			plan_fill_bottom(hp, B, n, src, dst, p->d_consts, p->d_lane_tw, inverse, coset, one_coset);
+			if (launch_bottom(B, st)) return cuda_fail(cudaGetLastError(), "launch_bottom");
+		} else {
+			plan_fill_pass(hp, P, n, src, dst, p->d_consts, p->d_lane_tw, inverse, coset, one_coset);
+			if (launch_pass(P, st)) return cuda_fail(cudaGetLastError(), "launch_pass");
 		}
-		plan_fill_pass(hp, P, n, src, dst, p->d_consts, p->d_lane_tw, inverse, coset, one_coset);
-		if (launch_pass(P, st)) return cuda_fail(cudaGetLastError(), "launch_pass");
+		if (ev) CU(cudaEventRecord(ev[n + 1], st));
 	}
 	return B2NTT_OK;
 }
@@ -134,6 +142,24 @@ static int run(b2ntt_plan* p, const void* d_in, void* d_out, bool inverse, int c
 extern "C" int b2ntt_exec(b2ntt_plan* p, const void* d_in, void* d_out, void* stream) {
 	if (!p) return B2NTT_EINVAL;
 	return run(p, d_in, d_out, false, 0, (cudaStream_t)stream);
+}
+
+extern "C" int b2ntt_exec_profile(b2ntt_plan* p, const void* d_in, void* d_out, void* stream, float* pass_ms, int* pass_kind, int max_passes) {
+	if (!p || !pass_ms || max_passes < 1) return B2NTT_EINVAL;
+	if (p->hp.tiny) return B2NTT_EUNSUPPORTED;
+	const int np = (int)p->hp.passes.size();
+	if (np > max_passes || np > 15) return B2NTT_EINVAL;
+	CU(cudaSetDevice(p->device));
+	cudaEvent_t ev[16];
+	for (int i = 0; i <= np; i++) CU(cudaEventCreate(&ev[i]));
+	int rc = run(p, d_in, d_out, false, 0, (cudaStream_t)stream, false, ev);
+	if (rc == B2NTT_OK && cudaEventSynchronize(ev[np]) != cudaSuccess) rc = cuda_fail(cudaGetLastError(), "cudaEventSynchronize");
+	for (int i = 0; i < np && rc == B2NTT_OK; i++) {
+		if (cudaEventElapsedTime(&pass_ms[i], ev[i], ev[i + 1]) != cudaSuccess) rc = cuda_fail(cudaGetLastError(), "cudaEventElapsedTime");
+		if (pass_kind) pass_kind[i] = p->hp.passes[i].kind;
+	}
+	for (int i = 0; i <= np; i++) cudaEventDestroy(ev[i]);
+	return rc == B2NTT_OK ? np : rc;
 }
 
 extern "C" int b2ntt_exec_inverse(b2ntt_plan* p, const void* d_in, void* d_out, int coset, void* stream) {

@@ -61,6 +61,13 @@ int b2ntt_plan_destroy(b2ntt_plan* plan);
  * (additive_ntt.cuh:250-259).  d_out may equal d_in when log_rate == 0. */
 int b2ntt_exec(b2ntt_plan* plan, const void* d_in, void* d_out, void* stream);
 
+/* b2ntt_exec with CUDA events recorded on `stream` around every pass launch (measurement aid, no
+ * reference counterpart).  Synchronises; writes the device time of each pass in milliseconds to
+ * pass_ms[0..n) and, when pass_kind is not NULL, the kernel of each pass (0: b2::pass_kernel, the
+ * bundle pass through shared memory; 1: b2::upper_kernel, the warp-uniform-twiddle pass; 2: b2::bottom_kernel, the 512-line tile pass).  Returns the
+ * number of passes n (<= max_passes) or a negative error. */
+int b2ntt_exec_profile(b2ntt_plan* plan, const void* d_in, void* d_out, void* stream, float* pass_ms, int* pass_kind, int max_passes);
+
 /* Inverse of b2ntt_exec on ONE coset per column (no reference counterpart):
  * d_in = batch * 2^log_h evaluations on coset `coset`, d_out = batch * 2^log_h coefficients. */
 int b2ntt_exec_inverse(b2ntt_plan* plan, const void* d_in, void* d_out, int coset, void* stream);

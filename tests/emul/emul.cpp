@@ -37,7 +37,7 @@ static void run_upper(const UpperParams& P) {
 	const int T = kUpperWarps * 32;
 	for (uint64_t grp = 0; grp < P.n_groups; grp++) {
 		const UGroup c = upper_group(P, grp);
-		for (int t = 0; t < T; t++) upper_twiddles(P, sm, c, t);
+		for (int t = 0; t < T; t++) upper_twiddles(P, sm, c, t, P.consts);
 		for (int t = 0; t < T; t++) upper_leaves(P, sm, t, T);
 		if (P.k == 4) {
 			for (int t = 0; t < T; t++) upper_copy<false>(P, sm, c, 0, 16, t, T);
@@ -59,6 +59,34 @@ static void run_upper(const UpperParams& P) {
 	}
 }
 
+// lowest pass on 512-line tiles (b2_bottom.cuh): same phase functions as bottom_kernel
+template <bool INV>
+static void run_bottom(const BottomParams& B) {
+	std::vector<uint32_t> mem(bottom_smem_words() + 8);
+	BottomSmem bs = bottom_smem_view(mem.data());
+	const UpperParams& P = B.up;
+	const int T = kUpperWarps * 32, nline = 5 - B.batch_bits;
+	for (int t = 0; t < T; t++) bottom_prologue(B, bs, t, T, P.consts);
+	for (uint64_t grp = 0; grp < P.n_groups; grp++) {
+		const UGroup c = upper_group(P, grp);
+		for (int t = 0; t < T; t++) upper_twiddles(P, bs.us, c, t, P.consts), bottom_tile_tables(B, bs, c, t - 16, P.consts);
+		for (int t = 0; t < T; t++) upper_copy<false>(P, bs.us, c, 0, 16, t, T);
+		for (int t = 0; t < T; t++) upper_leaves(P, bs.us, t, T);
+		if (!INV) {
+			for (int t = 0; t < T; t++) upper_pair<false>(P, bs.us, t & 31, t >> 5, 2, 0, 3, true, false);
+			for (int t = 0; t < T; t++) upper_pair<false>(P, bs.us, t & 31, (t >> 5) << 2, 0, 0, 1, false, false);
+		}
+		for (int iter = 0; iter < 2; iter++)
+			for (int n = 0; n < nline; n++)
+				for (int t = 0; t < T; t++) bottom_phase_b<INV>(B, bs, t >> 5, t & 31, iter, n);
+		if (INV) {
+			for (int t = 0; t < T; t++) upper_pair<true>(P, bs.us, t & 31, (t >> 5) << 2, 0, 0, 1, false, false);
+			for (int t = 0; t < T; t++) upper_pair<true>(P, bs.us, t & 31, t >> 5, 2, 0, 3, false, true);
+		}
+		for (int t = 0; t < T; t++) upper_copy<true>(P, bs.us, c, 0, 16, t, T);
+	}
+}
+
 extern "C" int emul_antt_cta(int field_bits, int layout, int log_h, int log_rate, int batch, const uint32_t* in,
                              uint32_t* out, int inverse, int coset, int cta_threads, int group_lines) {
 	HostPlan hp;
@@ -66,9 +94,16 @@ extern "C" int emul_antt_cta(int field_bits, int layout, int log_h, int log_rate
 	if (hp.tiny) return -4;
 	PassParams P;
 	UpperParams U;
+	BottomParams B;
 	const int np = (int)hp.passes.size();
 	for (int n = 0; n < np; n++) {
-		if ((inverse ? hp.passes[np - 1 - n] : hp.passes[n]).kind == 1) {
+		const int kind = (inverse ? hp.passes[np - 1 - n] : hp.passes[n]).kind;
+		if (kind == 2) {
+			plan_fill_bottom(hp, B, n, in, out, hp.consts, hp.lane_tw, inverse != 0, coset);
+			if (inverse) run_bottom<true>(B); else run_bottom<false>(B);
+			continue;
+		}
+		if (kind == 1) {
 			plan_fill_upper(hp, U, n, in, out, hp.consts, inverse != 0, coset);
 			if (inverse) run_upper<true>(U); else run_upper<false>(U);
 			continue;
