@@ -261,20 +261,25 @@ B2_HD void upper_pair(const UpperParams& P, const UpperSmem& sm, int lane, int x
 }
 
 // ---- coalesced copies of super-lines: global <-> slots, 16-byte chunks ---------------------------------
-// chunk ch of a set of `nsl` super-lines: piece = ch & 7, line = (ch >> 3) & 31, super-line = ch >> 8
+// A thread keeps its 16-byte piece (tid & 7) and walks lines tid >> 3, + nthreads / 8, ... of every super-line,
+// so all addresses advance by constant strides (nthreads = 32 or 128).
 template <bool STORE>
 B2_HD void upper_copy(const UpperParams& P, const UpperSmem& sm, const UGroup& c, int slot_off, int nsl, int tid, int nthreads) {
-	const uint32_t* srow = P.src + (uint64_t)(c.row >> P.src_row_shift) * P.src_row_words;
-	uint32_t* drow = P.dst + (uint64_t)c.row * P.dst_row_words;
-#pragma unroll 4
-	for (int ch = tid; ch < nsl * 256; ch += nthreads) {
-		const int piece = ch & 7, ln = (ch >> 3) & 31, x = ch >> 8;
-		uint32_t* s = sm.slots + ((size_t)(slot_off + x) * 32 + ln) * kUSlotWords + piece * 4;
-		const uint64_t off = upper_line(P, c, x, ln) * 32 + piece * 4;
-		if (STORE)
-			copy16_s2g(drow + off, s);
-		else
-			copy16_g2s(s, srow + off);
+	const int piece = tid & 7, ln0 = tid >> 3, dl = nthreads >> 3, per = 256 / nthreads;
+	const uint64_t g0 = upper_line(P, c, 0, ln0) * 32 + piece * 4, gx = (uint64_t)32 << P.q0;
+	const uint32_t* gs = P.src + (uint64_t)(c.row >> P.src_row_shift) * P.src_row_words + g0;
+	uint32_t* gd = P.dst + (uint64_t)c.row * P.dst_row_words + g0;
+	uint32_t* s = sm.slots + ((size_t)slot_off * 32 + ln0) * kUSlotWords + piece * 4;
+#pragma unroll 2
+	for (int x = 0; x < nsl; x++) {
+#pragma unroll 2
+		for (int j = 0; j < per; j++) {
+			if (STORE)
+				copy16_s2g(gd + (size_t)j * dl * 32, s + (size_t)j * dl * kUSlotWords);
+			else
+				copy16_g2s(s + (size_t)j * dl * kUSlotWords, gs + (size_t)j * dl * 32);
+		}
+		gs += gx, gd += gx, s += 32 * kUSlotWords;
 	}
 }
 

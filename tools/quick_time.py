@@ -23,6 +23,8 @@ def time_plan(field_bits, log_h, log_rate=0, layout=0, batch=1, iters=5):
     bytes_alg = (plan.in_words + plan.out_words) * 4
     print(json.dumps(dict(field=field_bits, log_h=log_h, log_rate=log_rate, layout=layout, batch=batch, passes=plan.passes,
                           ms=round(ms, 4), gel_s=round(n_out / ms / 1e6, 3), alg_gbs=round(bytes_alg / ms / 1e6, 1))), flush=True)
+    if os.environ.get("B2_PASSES"):
+        print("   passes:", " ".join(f"{n.split('::')[1][:6]}={t:.2f}" for n, t in plan.exec_profile(x, y)), flush=True)
     plan.close()
 
 def main():
