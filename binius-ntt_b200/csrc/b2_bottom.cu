@@ -23,7 +23,9 @@ __global__ void __launch_bounds__(kUpperWarps * 32, 2) bottom_kernel(const __gri
 #pragma unroll 1
 	for (uint64_t grp = g0; grp < g1; grp++) {
 		const UGroup c = upper_group(P, grp);  // hi = tile index of the row
-		upper_copy<false>(P, bs.us, c, 0, 16, tid, T);  // cp.async in flight while the tables are built
+		// every warp moves its own quad: forward the quad of phase A's first layer pair (x = warp + 4i), inverse the
+		// super-lines 4 warp .. 4 warp + 3 of phase B; cp.async stays in flight while the tables are built
+		upper_copy<false>(P, bs.us, c, 0, INV ? warp << 2 : warp, INV ? 1 : 4, 4, lane, 32);
 		upper_twiddles(P, bs.us, c, tid, bs.us.consts);
 		bottom_tile_tables(B, bs, c, tid - 16, bs.us.consts);
 		__syncthreads();
@@ -49,9 +51,9 @@ __global__ void __launch_bounds__(kUpperWarps * 32, 2) bottom_kernel(const __gri
 			__syncthreads();
 			upper_pair<true>(P, bs.us, lane, warp, 2, 0, 3, false, true);
 		}
-		__syncthreads();
-		upper_copy<true>(P, bs.us, c, 0, 16, tid, T);
-		__syncthreads();
+		__syncwarp();
+		upper_copy<true>(P, bs.us, c, 0, INV ? warp : warp << 2, INV ? 4 : 1, 4, lane, 32);
+		__syncthreads();  // the slots and the tables are free again
 	}
 }
 

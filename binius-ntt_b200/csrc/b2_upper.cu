@@ -38,27 +38,33 @@ __global__ void __launch_bounds__(kUpperWarps * 32, 2) upper_kernel(const __grid
 #pragma unroll 1
 	for (uint64_t grp = g0; grp < g1; grp++) {
 		const UGroup c = upper_group(P, grp);
-		upper_copy<false>(P, sm, c, slot_off, nsl, wt, wn);  // cp.async in flight while the tables are built
+		// every warp moves its own quad of super-lines (k = 4: the quad of its first layer pair in, the quad of its
+		// last layer pair out; k = 2: the whole group), so copies need no CTA barrier and overlap other warps' logic
+		const bool high_first = k4 && !INV;
+		upper_copy<false>(P, sm, c, slot_off, k4 ? (high_first ? warp : warp << 2) : 0, high_first ? 4 : 1, 4, lane, 32);
 		const uint64_t nk = ((uint64_t)c.row << 40) ^ c.hi;
 		if (nk != key) {  // uniform over the worker
 			key = nk;
 			upper_twiddles(P, sm, c, wt, sm.consts);
 			sync();
 			upper_leaves(P, sm, wt, wn);
+			sync();
 		}
 		copy_wait_all();
-		sync();
-		// k = 4, forward: bits (3,2) on the quads x = a << 2 | warp, then bits (1,0) on x = warp << 2 | a; inverse: the reverse.
-		// k = 2: bits (1,0) on the warp's own 4 super-lines.
+		__syncwarp();
 		const int nph = k4 ? 2 : 1;
 #pragma unroll 1
 		for (int ph = 0; ph < nph; ph++) {
 			const bool high = k4 && (INV ? ph == 1 : ph == 0);
 			upper_pair<INV>(P, sm, lane, high ? warp : (k4 ? warp << 2 : 0), high ? 2 : 0, slot_off, high ? 3 : 1, ph == 0, ph == nph - 1);
-			sync();
+			if (ph + 1 < nph)
+				__syncthreads();
+			else
+				__syncwarp();
 		}
-		upper_copy<true>(P, sm, c, slot_off, nsl, wt, wn);
-		sync();
+		const bool high_last = k4 && INV;
+		upper_copy<true>(P, sm, c, slot_off, k4 ? (high_last ? warp : warp << 2) : 0, high_last ? 4 : 1, 4, lane, 32);
+		sync();  // the slots are free again
 	}
 }
 

@@ -261,15 +261,16 @@ B2_HD void upper_pair(const UpperParams& P, const UpperSmem& sm, int lane, int x
 }
 
 // ---- coalesced copies of super-lines: global <-> slots, 16-byte chunks ---------------------------------
-// A thread keeps its 16-byte piece (tid & 7) and walks lines tid >> 3, + nthreads / 8, ... of every super-line,
-// so all addresses advance by constant strides (nthreads = 32 or 128).
+// Copies the nsl super-lines x = x0, x0 + xstep, ... of the group between global memory and the slots slot_off + x.
+// A thread keeps its 16-byte piece (tid & 7) and walks lines tid >> 3, + nthreads / 8, ... of every super-line, so all
+// addresses advance by constant strides (nthreads = 32: one warp moves its own quad; 128: the CTA moves the group).
 template <bool STORE>
-B2_HD void upper_copy(const UpperParams& P, const UpperSmem& sm, const UGroup& c, int slot_off, int nsl, int tid, int nthreads) {
+B2_HD void upper_copy(const UpperParams& P, const UpperSmem& sm, const UGroup& c, int slot_off, int x0, int xstep, int nsl, int tid, int nthreads) {
 	const int piece = tid & 7, ln0 = tid >> 3, dl = nthreads >> 3, per = 256 / nthreads;
-	const uint64_t g0 = upper_line(P, c, 0, ln0) * 32 + piece * 4, gx = (uint64_t)32 << P.q0;
+	const uint64_t g0 = upper_line(P, c, x0, ln0) * 32 + piece * 4, gx = ((uint64_t)32 << P.q0) * xstep;
 	const uint32_t* gs = P.src + (uint64_t)(c.row >> P.src_row_shift) * P.src_row_words + g0;
 	uint32_t* gd = P.dst + (uint64_t)c.row * P.dst_row_words + g0;
-	uint32_t* s = sm.slots + ((size_t)slot_off * 32 + ln0) * kUSlotWords + piece * 4;
+	uint32_t* s = sm.slots + ((size_t)(slot_off + x0) * 32 + ln0) * kUSlotWords + piece * 4;
 #pragma unroll 2
 	for (int x = 0; x < nsl; x++) {
 #pragma unroll 2
@@ -279,7 +280,7 @@ B2_HD void upper_copy(const UpperParams& P, const UpperSmem& sm, const UGroup& c
 			else
 				copy16_g2s(s + (size_t)j * dl * kUSlotWords, gs + (size_t)j * dl * 32);
 		}
-		gs += gx, gd += gx, s += 32 * kUSlotWords;
+		gs += gx, gd += gx, s += (size_t)xstep * 32 * kUSlotWords;
 	}
 }
 

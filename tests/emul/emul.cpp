@@ -40,7 +40,7 @@ static void run_upper(const UpperParams& P) {
 		for (int t = 0; t < T; t++) upper_twiddles(P, sm, c, t, P.consts);
 		for (int t = 0; t < T; t++) upper_leaves(P, sm, t, T);
 		if (P.k == 4) {
-			for (int t = 0; t < T; t++) upper_copy<false>(P, sm, c, 0, 16, t, T);
+			for (int t = 0; t < T; t++) upper_copy<false>(P, sm, c, 0, 0, 1, 16, t, T);
 			for (int t = 0; t < T; t++) {
 				if (!INV) upper_pair<INV>(P, sm, t & 31, t >> 5, 2, 0, 3, true, false);
 				else upper_pair<INV>(P, sm, t & 31, (t >> 5) << 2, 0, 0, 1, true, false);
@@ -49,12 +49,12 @@ static void run_upper(const UpperParams& P) {
 				if (!INV) upper_pair<INV>(P, sm, t & 31, (t >> 5) << 2, 0, 0, 1, false, true);
 				else upper_pair<INV>(P, sm, t & 31, t >> 5, 2, 0, 3, false, true);
 			}
-			for (int t = 0; t < T; t++) upper_copy<true>(P, sm, c, 0, 16, t, T);
+			for (int t = 0; t < T; t++) upper_copy<true>(P, sm, c, 0, 0, 1, 16, t, T);
 		} else {
 			const int w = (int)(grp & 3);  // any warp slot
-			for (int t = 0; t < 32; t++) upper_copy<false>(P, sm, c, w * 4, 4, t, 32);
+			for (int t = 0; t < 32; t++) upper_copy<false>(P, sm, c, w * 4, 0, 1, 4, t, 32);
 			for (int t = 0; t < 32; t++) upper_pair<INV>(P, sm, t, 0, 0, w * 4, 1, true, true);
-			for (int t = 0; t < 32; t++) upper_copy<true>(P, sm, c, w * 4, 4, t, 32);
+			for (int t = 0; t < 32; t++) upper_copy<true>(P, sm, c, w * 4, 0, 1, 4, t, 32);
 		}
 	}
 }
@@ -70,7 +70,7 @@ static void run_bottom(const BottomParams& B) {
 	for (uint64_t grp = 0; grp < P.n_groups; grp++) {
 		const UGroup c = upper_group(P, grp);
 		for (int t = 0; t < T; t++) upper_twiddles(P, bs.us, c, t, P.consts), bottom_tile_tables(B, bs, c, t - 16, P.consts);
-		for (int t = 0; t < T; t++) upper_copy<false>(P, bs.us, c, 0, 16, t, T);
+		for (int t = 0; t < T; t++) upper_copy<false>(P, bs.us, c, 0, 0, 1, 16, t, T);
 		for (int t = 0; t < T; t++) upper_leaves(P, bs.us, t, T);
 		if (!INV) {
 			for (int t = 0; t < T; t++) upper_pair<false>(P, bs.us, t & 31, t >> 5, 2, 0, 3, true, false);
@@ -83,7 +83,7 @@ static void run_bottom(const BottomParams& B) {
 			for (int t = 0; t < T; t++) upper_pair<true>(P, bs.us, t & 31, (t >> 5) << 2, 0, 0, 1, false, false);
 			for (int t = 0; t < T; t++) upper_pair<true>(P, bs.us, t & 31, t >> 5, 2, 0, 3, false, true);
 		}
-		for (int t = 0; t < T; t++) upper_copy<true>(P, bs.us, c, 0, 16, t, T);
+		for (int t = 0; t < T; t++) upper_copy<true>(P, bs.us, c, 0, 0, 1, 16, t, T);
 	}
 }
 
