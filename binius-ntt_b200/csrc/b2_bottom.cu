@@ -9,50 +9,56 @@
 namespace b2 {
 
 template <bool INV>
-__global__ void __launch_bounds__(kUpperWarps * 32, 2) bottom_kernel(const __grid_constant__ BottomParams B) {
+__global__ void __launch_bounds__(kBottomTeams * 128, 1) bottom_kernel(const __grid_constant__ BottomParams B) {
 	extern __shared__ __align__(16) uint32_t bsmem_raw[];
-	BottomSmem bs = bottom_smem_view(bsmem_raw);
+	const int team = threadIdx.x >> 7, tid = threadIdx.x & 127, warp = tid >> 5, lane = tid & 31, T = 128;
+	BottomSmem bs = bottom_smem_view(bsmem_raw, team);
 	const UpperParams& P = B.up;
-	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, T = kUpperWarps * 32;
 	const int nline = 5 - B.batch_bits;
-	for (int i = tid; i < 1024; i += T) bs.us.consts[i] = P.consts[i];
+	for (int i = threadIdx.x; i < 1024; i += kBottomTeams * 128) bs.us.consts[i] = P.consts[i];
 	__syncthreads();
-	bottom_prologue(B, bs, tid, T, bs.us.consts);
+	bottom_prologue(B, bs, (int)threadIdx.x, kBottomTeams * 128, bs.us.consts);
 	const uint64_t per = (P.n_groups + gridDim.x - 1) / gridDim.x;
 	const uint64_t g0 = per * blockIdx.x, g1 = g0 + per < P.n_groups ? g0 + per : P.n_groups;
 #pragma unroll 1
-	for (uint64_t grp = g0; grp < g1; grp++) {
-		const UGroup c = upper_group(P, grp);  // hi = tile index of the row
-		// every warp moves its own quad: forward the quad of phase A's first layer pair (x = warp + 4i), inverse the
-		// super-lines 4 warp .. 4 warp + 3 of phase B; cp.async stays in flight while the tables are built
-		upper_copy<false>(P, bs.us, c, 0, INV ? warp << 2 : warp, INV ? 1 : 4, 4, lane, 32);
-		upper_twiddles(P, bs.us, c, tid, bs.us.consts);
-		bottom_tile_tables(B, bs, c, tid - 16, bs.us.consts);
+	for (uint64_t gg = g0; gg < g1; gg += kBottomTeams) {
+		const uint64_t grp = gg + team;
+		const bool active = grp < g1;  // uniform over the team; every barrier below is met by all warps of the CTA
+		const UGroup c = upper_group(P, active ? grp : gg);  // hi = tile index of the row
+		if (active) {
+			// every warp moves its own quad: forward the quad of phase A's first layer pair (x = warp + 4i), inverse the
+			// super-lines 4 warp .. 4 warp + 3 of phase B; cp.async stays in flight while the tables are built
+			upper_copy<false>(P, bs.us, c, 0, INV ? warp << 2 : warp, INV ? 1 : 4, 4, lane, 32);
+			upper_twiddles(P, bs.us, c, tid, bs.us.consts);
+			bottom_tile_tables(B, bs, c, tid - 16, bs.us.consts);
+		}
 		__syncthreads();
-		upper_leaves(P, bs.us, tid, T);
+		if (active) upper_leaves(P, bs.us, tid, T);
 		copy_wait_all();
 		__syncthreads();
 		if (!INV) {
-			upper_pair<false>(P, bs.us, lane, warp, 2, 0, 3, true, false);
+			if (active) upper_pair<false>(P, bs.us, lane, warp, 2, 0, 3, true, false);
 			__syncthreads();
-			upper_pair<false>(P, bs.us, lane, warp << 2, 0, 0, 1, false, false);
+			if (active) upper_pair<false>(P, bs.us, lane, warp << 2, 0, 0, 1, false, false);
 			__syncwarp();
 		}
+		if (active) {
 #pragma unroll 1
-		for (int iter = 0; iter < 2; iter++) {
+			for (int iter = 0; iter < 2; iter++) {
 #pragma unroll 1
-			for (int n = 0; n < nline; n++) {
-				bottom_phase_b<INV>(B, bs, warp, lane, iter, n);
-				__syncwarp();
+				for (int n = 0; n < nline; n++) {
+					bottom_phase_b<INV>(B, bs, warp, lane, iter, n);
+					__syncwarp();
+				}
 			}
 		}
 		if (INV) {
-			upper_pair<true>(P, bs.us, lane, warp << 2, 0, 0, 1, false, false);
+			if (active) upper_pair<true>(P, bs.us, lane, warp << 2, 0, 0, 1, false, false);
 			__syncthreads();
-			upper_pair<true>(P, bs.us, lane, warp, 2, 0, 3, false, true);
+			if (active) upper_pair<true>(P, bs.us, lane, warp, 2, 0, 3, false, true);
 		}
 		__syncwarp();
-		upper_copy<true>(P, bs.us, c, 0, INV ? warp : warp << 2, INV ? 4 : 1, 4, lane, 32);
+		if (active) upper_copy<true>(P, bs.us, c, 0, INV ? warp : warp << 2, INV ? 4 : 1, 4, lane, 32);
 		__syncthreads();  // the slots and the tables are free again
 	}
 }
@@ -64,10 +70,11 @@ static int launch_bottom_t(const BottomParams& B, cudaStream_t stream) {
 	cudaGetDevice(&dev);
 	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
 	cudaFuncSetAttribute(bottom_kernel<INV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-	uint64_t ctas = (uint64_t)sms * 2 * 4;
-	if (ctas > B.up.n_groups) ctas = B.up.n_groups;
+	uint64_t ctas = (uint64_t)sms * 4;  // one CTA of two teams per SM, a few chunks each for balance
+	const uint64_t pairs = (B.up.n_groups + kBottomTeams - 1) / kBottomTeams;
+	if (ctas > pairs) ctas = pairs;
 	if (ctas == 0) return -1;
-	bottom_kernel<INV><<<(unsigned)ctas, kUpperWarps * 32, smem, stream>>>(B);
+	bottom_kernel<INV><<<(unsigned)ctas, kBottomTeams * 128, smem, stream>>>(B);
 	return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 

@@ -23,7 +23,6 @@ struct BottomParams {
 	uint8_t cls[32];         // twiddle class per stage
 };
 
-// shared-memory image after the upper part: [TL 512][TH 8][IH 8][IL 5*512][lane_tw 160]
 struct BottomSmem {
 	UpperSmem us;
 	uint32_t* TL;   // line-layer twiddle, tile-independent part: heap order, bit b owns [2^(8-b), 2^(9-b)) - index (1 << (8-b)) + (l >> (b+1))
@@ -32,15 +31,25 @@ struct BottomSmem {
 	uint32_t* IL;   // [n_inline][512] in-line twiddle by local line
 	uint32_t* LT;   // [5][32] lane_tw copy
 };
-B2_HD size_t bottom_smem_words() { return upper_smem_words(4) + 512 + 8 + 8 + 5 * 512 + 160; }
-B2_HD BottomSmem bottom_smem_view(uint32_t* base) {
+// One CTA runs kBottomTeams teams of 4 warps, each on its own tile.  Warps w and w + 4 share an SM sub-partition and
+// meet at the same CTA barriers, so they execute the same stretch of straight-line butterfly code at the same time:
+// the instruction cache serves both (two independent CTAs per SM ran out of phase and stalled on instruction fetch).
+// layout: [consts 1024][TL 512][IL 5*512][LT 160]  then per team  [leaves 15*81*4][tw 16][TH 8][IH 8][slots 16*32*36]
+constexpr int kBottomTeams = 2;
+B2_HD size_t bottom_team_words() { return (size_t)kUpperMaxTw * kLeafPitch + 16 + 8 + 8 + (size_t)16 * 32 * kUSlotWords; }
+B2_HD size_t bottom_smem_words() { return 1024 + 512 + 5 * 512 + 160 + kBottomTeams * bottom_team_words(); }
+B2_HD BottomSmem bottom_smem_view(uint32_t* base, int team = 0) {
 	BottomSmem b;
-	b.us = upper_smem_view(base);
-	b.TL = base + upper_smem_words(4);
-	b.TH = b.TL + 512;
-	b.IH = b.TH + 8;
-	b.IL = b.IH + 8;
+	b.us.consts = base;
+	b.TL = base + 1024;
+	b.IL = b.TL + 512;
 	b.LT = b.IL + 5 * 512;
+	uint32_t* t = b.LT + 160 + (size_t)team * bottom_team_words();
+	b.us.leaves = reinterpret_cast<Mask4*>(t);
+	b.us.tw = t + kUpperMaxTw * kLeafPitch;
+	b.TH = b.us.tw + 16;
+	b.IH = b.TH + 8;
+	b.us.slots = b.IH + 8;
 	return b;
 }
 
