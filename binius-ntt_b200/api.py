@@ -38,6 +38,7 @@ def lib():
         L.b2ntt_exec.argtypes = [vp, vp, vp, vp]
         L.b2ntt_exec_inverse.argtypes = [vp, vp, vp, i, vp]
         L.b2ntt_exec_host.argtypes = [vp, vp, sz, vp]
+        L.b2ntt_exec_host_batch.argtypes = [vp, vp, sz, vp, i]
         L.b2ntt_exec_profile.argtypes = [vp, vp, vp, vp, vp, vp, i]
         L.b2ntt_exec_coset.argtypes = [vp, vp, vp, i, vp]
         L.b2ntt_exec_top.argtypes = [vp, vp, i, vp]
@@ -170,6 +171,22 @@ class Plan:
         n_in = a.size // self.limbs // self.batch if a.size % (self.limbs * self.batch) == 0 else 0
         _check(lib().b2ntt_exec_host(self._h, a.ctypes.data, n_in, o.ctypes.data), "b2ntt_exec_host")
         return h_out
+
+
+def _exec_host_batch(self, h_ins, h_outs):
+    """Pipelined host path: len(h_ins) independent transforms, H2D / kernels / D2H overlapped on three streams."""
+    ins = [_host_words(x) for x in h_ins]
+    outs = [_host_words(x) for x in h_outs]
+    if len(ins) != len(outs) or any(o.size != self.out_words for o in outs) or any(a.size != self.in_words for a in ins):
+        raise ValueError("exec_host_batch: wrong sizes")
+    n = len(ins)
+    pin = (C.c_void_p * n)(*[a.ctypes.data for a in ins])
+    pout = (C.c_void_p * n)(*[o.ctypes.data for o in outs])
+    _check(lib().b2ntt_exec_host_batch(self._h, pin, self.in_words // self.limbs // self.batch, pout, n), "b2ntt_exec_host_batch")
+    return h_outs
+
+
+Plan.exec_host_batch = _exec_host_batch
 
 
 def _host_words(x):

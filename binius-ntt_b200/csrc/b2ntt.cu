@@ -36,6 +36,13 @@ struct b2ntt_plan {
 	cudaStream_t stream = nullptr;
 	uint32_t* d_in = nullptr;
 	uint32_t* d_out = nullptr;
+	// exec_host_batch pipeline: 3 buffer sets, 3 streams (H2D, transform, D2H)
+	static constexpr int kPipe = 3;
+	cudaStream_t ps[3] = {nullptr, nullptr, nullptr};
+	uint32_t* pd_in[kPipe] = {nullptr, nullptr, nullptr};
+	uint32_t* pd_out[kPipe] = {nullptr, nullptr, nullptr};
+	cudaEvent_t ev_in[kPipe] = {}, ev_cmp[kPipe] = {}, ev_out[kPipe] = {};
+	bool pipe_ready = false;
 };
 
 static size_t elem_words(const HostPlan& hp) { return (size_t)1 << hp.limbs_log; }
@@ -84,6 +91,15 @@ extern "C" int b2ntt_plan_destroy(b2ntt_plan* p) {
 	if (p->d_in) cudaFree(p->d_in);
 	if (p->d_out) cudaFree(p->d_out);
 	if (p->stream) cudaStreamDestroy(p->stream);
+	for (int i = 0; i < b2ntt_plan::kPipe; i++) {
+		if (p->pd_in[i]) cudaFree(p->pd_in[i]);
+		if (p->pd_out[i]) cudaFree(p->pd_out[i]);
+		if (p->ev_in[i]) cudaEventDestroy(p->ev_in[i]);
+		if (p->ev_cmp[i]) cudaEventDestroy(p->ev_cmp[i]);
+		if (p->ev_out[i]) cudaEventDestroy(p->ev_out[i]);
+	}
+	for (int i = 0; i < 3; i++)
+		if (p->ps[i]) cudaStreamDestroy(p->ps[i]);
 	delete p;
 	return B2NTT_OK;
 }
@@ -204,6 +220,49 @@ extern "C" int b2ntt_exec_host(b2ntt_plan* p, const void* h_in, size_t n_in, voi
 	if (rc) return rc;
 	CU(cudaMemcpyAsync(h_out, p->d_out, ob, cudaMemcpyDeviceToHost, p->stream));
 	CU(cudaStreamSynchronize(p->stream));
+	return B2NTT_OK;
+}
+
+// Pipelined host path: transform i is copied in on one stream while transform i-1 runs on a second and transform
+// i-2 is copied out on a third (PCIe is full duplex), three device buffer sets in rotation.
+extern "C" int b2ntt_exec_host_batch(b2ntt_plan* p, const void* const* h_in, size_t n_in, void* const* h_out, int count) {
+	if (!p || !h_in || !h_out || count < 0) return B2NTT_EINVAL;
+	const HostPlan& hp = p->hp;
+	if (n_in != ((size_t)1 << hp.log_h)) return B2NTT_EINVAL;
+	for (int i = 0; i < count; i++)
+		if (!h_in[i] || !h_out[i]) return B2NTT_EINVAL;
+	if (count == 0) return B2NTT_OK;
+	CU(cudaSetDevice(p->device));
+	const size_t ib = in_words(hp) * 4, ob = out_words(hp) * 4;
+	constexpr int K = b2ntt_plan::kPipe;
+	if (!p->pipe_ready) {
+		for (int i = 0; i < 3; i++) CU(cudaStreamCreateWithFlags(&p->ps[i], cudaStreamNonBlocking));
+		for (int i = 0; i < K; i++) {
+			cudaError_t e = cudaMalloc(&p->pd_out[i], ob);
+			if (e == cudaSuccess && hp.log_rate) e = cudaMalloc(&p->pd_in[i], ib);
+			if (e != cudaSuccess) return e == cudaErrorMemoryAllocation ? (cudaGetLastError(), B2NTT_ENOMEM) : cuda_fail(e, "cudaMalloc");
+			CU(cudaEventCreateWithFlags(&p->ev_in[i], cudaEventDisableTiming));
+			CU(cudaEventCreateWithFlags(&p->ev_cmp[i], cudaEventDisableTiming));
+			CU(cudaEventCreateWithFlags(&p->ev_out[i], cudaEventDisableTiming));
+		}
+		p->pipe_ready = true;
+	}
+	for (int i = 0; i < count; i++) {
+		const int b = i % K;
+		uint32_t* din = hp.log_rate ? p->pd_in[b] : p->pd_out[b];
+		if (i >= K) CU(cudaStreamWaitEvent(p->ps[0], p->ev_out[b], 0));  // the buffer set is free again
+		CU(cudaMemcpyAsync(din, h_in[i], ib, cudaMemcpyHostToDevice, p->ps[0]));
+		CU(cudaEventRecord(p->ev_in[b], p->ps[0]));
+		CU(cudaStreamWaitEvent(p->ps[1], p->ev_in[b], 0));
+		const int rc = run(p, din, p->pd_out[b], false, 0, p->ps[1]);
+		if (rc) return rc;
+		CU(cudaEventRecord(p->ev_cmp[b], p->ps[1]));
+		CU(cudaStreamWaitEvent(p->ps[2], p->ev_cmp[b], 0));
+		CU(cudaMemcpyAsync(h_out[i], p->pd_out[b], ob, cudaMemcpyDeviceToHost, p->ps[2]));
+		CU(cudaEventRecord(p->ev_out[b], p->ps[2]));
+	}
+	CU(cudaStreamSynchronize(p->ps[2]));
+	CU(cudaStreamSynchronize(p->ps[0]));
 	return B2NTT_OK;
 }
 

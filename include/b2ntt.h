@@ -91,6 +91,14 @@ int b2ntt_exec_top(b2ntt_plan* plan, void* d_buf, int log_segments, void* stream
  * element count per column and must equal 2^log_h (else B2NTT_EINVAL, apply()'s `return false`). */
 int b2ntt_exec_host(b2ntt_plan* plan, const void* h_in, size_t n_in, void* h_out);
 
+/* `count` independent calls of AdditiveNTT::apply in one pipelined call: the host-to-device copy of transform i,
+ * the kernels of transform i-1 and the device-to-host copy of transform i-2 run on three streams over three
+ * device buffer sets (PCIe is full duplex), so the host path runs at the speed of the slowest of the three
+ * instead of their sum.  h_in[i] / h_out[i]: host buffers as for b2ntt_exec_host (pinned memory for full speed;
+ * h_out[i] must not be read before the call returns; buffers may repeat among i only if that is harmless to the
+ * caller).  Synchronises before returning.  No reference counterpart (apply() is one blocking call, :262). */
+int b2ntt_exec_host_batch(b2ntt_plan* plan, const void* const* h_in, size_t n_in, void* const* h_out, int count);
+
 /* Query: number of kernel launches one b2ntt_exec issues, and HBM passes over the data set. */
 int b2ntt_plan_launches(const b2ntt_plan* plan);
 int b2ntt_plan_passes(const b2ntt_plan* plan);

@@ -142,3 +142,17 @@ def test_error_paths(b2, cuda):
     good.order = b2.DataOrder.BIT_REVERSED
     assert ntt.apply(good, out) is False
     assert b2.check_gpu_capabilities(0)
+
+
+@pytest.mark.gpu
+def test_exec_host_batch_matches_exec_host(b2, oracle, cuda):
+    """the pipelined host path gives the same bytes as AdditiveNTT::apply, in order, with buffer sets reused"""
+    for field_bits, log_h, r in [(32, 14, 2), (128, 13, 0)]:
+        limbs = field_bits // 32
+        p = b2.Plan(field_bits, log_h, r)
+        xs = [np.random.default_rng(40 + i).integers(0, 2**32, size=(1 << log_h) * limbs, dtype=np.uint32) for i in range(7)]
+        outs = [np.zeros(p.out_words, dtype=np.uint32) for _ in xs]
+        p.exec_host_batch(xs, outs)
+        for x, o in zip(xs, outs):
+            assert np.array_equal(o, oracle.antt_forward(x, log_h, r, limbs))
+        p.close()
