@@ -181,38 +181,61 @@ __device__ __forceinline__ void sliced64_mul_from(const uint32_t* a0p, const uin
 	}
 }
 
+// 32 blocks (16 KB per operand) per CTA iteration: operands come in by coalesced cp.async into padded rows (pitch 132
+// words: a quarter warp reading 16 bytes of 8 different rows hits 8 different bank groups), the three GF(2^64)
+// sub-products of a block go to three threads, are combined through shared memory, and the result rows leave by
+// coalesced 16-byte stores.
+constexpr int kMulPitch = 132;
 __global__ void __launch_bounds__(96) mul_sliced128_kernel(const uint32_t* __restrict__ a, const uint32_t* __restrict__ b, uint32_t* __restrict__ o, uint64_t n_blocks) {
 	// 96 threads = 32 blocks x 3 sub-products; thread (blk, q): q = threadIdx.x / 32
-	__shared__ uint32_t sm[3][32][65];
+	extern __shared__ __align__(16) uint32_t msm[];
+	uint32_t* sa = msm;                       // [32][132] operand a, later the result rows
+	uint32_t* sb = msm + 32 * kMulPitch;      // [32][132] operand b
+	uint32_t* sz = sb + 32 * kMulPitch;       // [3][32][65] sub-products
 	const int q = threadIdx.x >> 5, lb = threadIdx.x & 31;
 	for (uint64_t g0 = (uint64_t)blockIdx.x * 32; g0 < n_blocks; g0 += (uint64_t)gridDim.x * 32) {
-		const uint64_t g = g0 + lb;
-		const bool act = g < n_blocks;
-		uint32_t r[64];
+		const int nact = n_blocks - g0 < 32 ? (int)(n_blocks - g0) : 32;
+		for (int ch = threadIdx.x; ch < nact * 32; ch += 96) {  // 16-byte chunks: 32 per block row
+			const int row = ch >> 5, c4 = (ch & 31) * 4;
+			const unsigned da = (unsigned)__cvta_generic_to_shared(sa + row * kMulPitch + c4), db = (unsigned)__cvta_generic_to_shared(sb + row * kMulPitch + c4);
+			asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(da), "l"(a + (g0 + row) * 128 + c4) : "memory");
+			asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(db), "l"(b + (g0 + row) * 128 + c4) : "memory");
+		}
+		asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+		__syncthreads();
+		const bool act = lb < nact;
 		if (act) {
-			const uint32_t *pa = a + g * 128, *pb = b + g * 128;
+			uint32_t r[64];
+			const uint32_t *pa = sa + lb * kMulPitch, *pb = sb + lb * kMulPitch;
 			if (q == 0) sliced64_mul_from(pa, pa, pb, pb, false, 0, r);        // Z0 = A0*B0
 			else if (q == 1) sliced64_mul_from(pa, pa, pb, pb, false, 2, r);   // Z2 = A1*B1
 			else sliced64_mul_from(pa, pa + 64, pb, pb + 64, true, 0, r);      // ZZ = (A0+A1)*(B0+B1)
 #pragma unroll
-			for (int i = 0; i < 64; i++) sm[q][lb][i] = r[i];
+			for (int i = 0; i < 64; i++) sz[(q * 32 + lb) * 65 + i] = r[i];
 		}
 		__syncthreads();
 		if (act) {
-			// lo = Z0 + Z2 ; hi = ZZ + Z0 + Z2 + alpha6 * Z2 ; each thread writes a third of the words
-			uint32_t* po = o + g * 128;
+			// lo = Z0 + Z2 ; hi = ZZ + Z0 + Z2 + alpha6 * Z2 ; result rows replace operand a
+			const uint32_t *z0 = sz + lb * 65, *z2p = sz + (32 + lb) * 65, *zz = sz + (64 + lb) * 65;
+			uint32_t* po = sa + lb * kMulPitch;
 			if (q == 0) {
-				for (int i = 0; i < 64; i++) po[i] = sm[0][lb][i] ^ sm[1][lb][i];
+				for (int i = 0; i < 64; i++) po[i] = z0[i] ^ z2p[i];
 			} else if (q == 1) {
 				uint32_t z2[64], az[64];
-				for (int i = 0; i < 64; i++) z2[i] = sm[1][lb][i];
+				for (int i = 0; i < 64; i++) z2[i] = z2p[i];
 				Sliced<6>::mul_alpha(z2, az);
-				for (int i = 0; i < 64; i++) po[64 + i] = sm[2][lb][i] ^ sm[0][lb][i] ^ z2[i] ^ az[i];
+				for (int i = 0; i < 64; i++) po[64 + i] = zz[i] ^ z0[i] ^ z2[i] ^ az[i];
 			}
+		}
+		__syncthreads();
+		for (int ch = threadIdx.x; ch < nact * 32; ch += 96) {
+			const int row = ch >> 5, c4 = (ch & 31) * 4;
+			*reinterpret_cast<uint4*>(o + (g0 + row) * 128 + c4) = *reinterpret_cast<const uint4*>(sa + row * kMulPitch + c4);
 		}
 		__syncthreads();
 	}
 }
+constexpr size_t kMulSmemBytes = (2 * 32 * kMulPitch + 3 * 32 * 65) * sizeof(uint32_t);
 
 int launch_mul(int field_bits, int layout, const uint32_t* a, const uint32_t* b, uint32_t* o, uint64_t n, cudaStream_t stream) {
 	if (n == 0) return 0;
@@ -239,7 +262,8 @@ int launch_mul(int field_bits, int layout, const uint32_t* a, const uint32_t* b,
 		} else if (field_bits == 128) {
 			unsigned blocks = (unsigned)((nb + 31) / 32);
 			if (blocks > cap) blocks = cap;
-			mul_sliced128_kernel<<<blocks, 96, 0, stream>>>(a, b, o, nb);
+			cudaFuncSetAttribute(mul_sliced128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMulSmemBytes);
+			mul_sliced128_kernel<<<blocks, 96, kMulSmemBytes, stream>>>(a, b, o, nb);
 		} else
 			return -1;
 	}
