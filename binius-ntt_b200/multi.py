@@ -65,6 +65,15 @@ class ColumnShardedRS:
             return d_in if d_out is None else d_out
         return self.plan.exec(d_in, d_out, stream)
 
+    def encode_from_evaluations(self, d_evals, d_out=None, stream=None):
+        """Systematic (interpolate-then-extend) encode, SURVEY 8f.1: d_evals holds this rank's columns as evaluations
+        on coset 0; the inverse transform (v ^= u; u ^= w*v, stages low to high) recovers the novel-basis coefficients,
+        the forward transform evaluates them on every coset.  Row 0 of each output column equals the input column."""
+        if not self.plan:
+            return d_evals if d_out is None else d_out
+        coeffs = self.plan.exec_inverse(d_evals, torch.empty_like(d_evals), 0, stream)
+        return self.plan.exec(coeffs, d_out, stream)
+
     def close(self):
         if self.plan:
             self.plan.close()

@@ -12,6 +12,8 @@
 
 #include "../../oracle/oracle.h"
 #include "ulvt/finite_fields/binary_tower.cuh"
+#include "ulvt/finite_fields/binary_tower_simd.cuh"
+#include "ulvt/finite_fields/circuit_generator/utils/utils.hpp"
 #include "ulvt/finite_fields/circuit_generator/unrolled/binary_tower_unrolled.cuh"
 #include "ulvt/ntt/additive_ntt.cuh"
 #include "ulvt/utils/bitslicing.cuh"
@@ -122,6 +124,32 @@ int main(int argc, char** argv) {
 		CHECK(memcmp(z.w, w, 16) == 0);
 	}
 	CHECK(FanPaarTowerField<5>::N_BITS() == 32 && FanPaarTowerField<3>::is_valid(0xff) && !FanPaarTowerField<3>::is_valid(0x100));
+
+	// ---- packed lanes (tests.cu:17-91 style) and the hex helpers (tests.cu:186-188) ----
+	for (int i = 0; i < 500; i++) {
+		const uint32_t a = gen(), b = gen();
+		CHECK(mul_binary_tower_32b_simd<0>(a, b) == orc_mul_packed32(a, b, 0));
+		CHECK(mul_binary_tower_32b_simd<2>(a, b) == orc_mul_packed32(a, b, 2));
+		CHECK(mul_binary_tower_32b_simd<3>(a, b) == orc_mul_packed32(a, b, 3));
+		CHECK(mul_binary_tower_32b_simd<4>(a, b) == orc_mul_packed32(a, b, 4));
+		CHECK(mul_binary_tower_32b_simd<5>(a, b) == orc_mul32(a, b));
+		uint32_t x = a, y = b;
+		orc_interleave32(&x, &y, 3);
+		const auto cd = interleave_32b<3>(a, b);
+		CHECK(cd.first == x && cd.second == y);
+		orc_interleave32(&(x = a), &(y = b), 0);
+		const auto cd0 = interleave_32b<0>(a, b);
+		CHECK(cd0.first == x && cd0.second == y);
+		const uint32_t xa = xor_adjacent_32b<2>(a);
+		CHECK(((xa >> 4) & 0x0f0f0f0fu) == (xa & 0x0f0f0f0fu) && (xa & 0x0f0f0f0fu) == ((a ^ (a >> 4)) & 0x0f0f0f0fu));
+	}
+	{
+		uint32_t w[4] = {0, 0, 0, 0};
+		write_string_to_int_arr(w, "0x0123456789abcdef0011223344556677");
+		CHECK(w[0] == 0x44556677u && w[1] == 0x00112233u && w[2] == 0x89abcdefu && w[3] == 0x01234567u);
+		CHECK(int_to_hex(0xbeefu) == "beef");
+		CHECK(sizeof(KERNEL_LAUNCH_CONFIGS) == 31 * 3 * 2 * sizeof(dim3));
+	}
 
 	// ---- bit-slicing and the bit-sliced products (tests.cu:125-201, test_fanpaartower.cu:127-273 style) ----
 	{

@@ -150,3 +150,16 @@ def test_column_sharded_rs_single_rank(b2, oracle, cuda):
     for c in range(6):
         assert np.array_equal(out[c << 14:(c + 1) << 14], oracle.antt_forward(x[c << 12:(c + 1) << 12], 12, 2, 1))
     rs.close()
+
+
+@pytest.mark.gpu
+def test_rs_encode_from_evaluations_is_systematic(b2, oracle, cuda):
+    rs = b2.ColumnShardedRS(3, 13, 2, field_bits=32)
+    y = np.random.default_rng(8).integers(0, 2**32, size=3 << 13, dtype=np.uint32)
+    out = rs.encode_from_evaluations(torch.from_numpy(y.view(np.int32).copy()).to(cuda)).cpu().numpy().view(np.uint32)
+    for c in range(3):
+        col = y[c << 13:(c + 1) << 13]
+        want = oracle.antt_forward(oracle.antt_inverse(col, 13, 2, 0, 1), 13, 2, 1)
+        assert np.array_equal(out[c << 15:(c + 1) << 15], want)
+        assert np.array_equal(out[c << 15:(c << 15) + (1 << 13)], col)  # coset 0 reproduces the message
+    rs.close()
