@@ -28,7 +28,7 @@ __global__ void __launch_bounds__(kBottomTeams * 128, 1) bottom_kernel(const __g
 		if (active) {
 			// every warp moves its own quad: forward the quad of phase A's first layer pair (x = warp + 4i), inverse the
 			// super-lines 4 warp .. 4 warp + 3 of phase B; cp.async stays in flight while the tables are built
-			upper_copy<false>(P, bs.us, c, 0, INV ? warp << 2 : warp, INV ? 1 : 4, 4, lane, 32);
+			upper_copy<false>(P, bs.us, c, 0, INV ? warp << 2 : warp, INV ? 1 : 4, 4, 0, 1, lane);
 			upper_twiddles(P, bs.us, c, tid, bs.us.consts);
 			bottom_tile_tables(B, bs, c, tid - 16, bs.us.consts);
 		}
@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(kBottomTeams * 128, 1) bottom_kernel(const __g
 			if (active) upper_pair<true>(P, bs.us, lane, warp, 2, 0, 3, false, true);
 		}
 		__syncwarp();
-		if (active) upper_copy<true>(P, bs.us, c, 0, INV ? warp : warp << 2, INV ? 4 : 1, 4, lane, 32);
+		if (active) upper_copy<true>(P, bs.us, c, 0, INV ? warp : warp << 2, INV ? 4 : 1, 4, 0, 1, lane);
 		__syncthreads();  // the slots and the tables are free again
 	}
 }

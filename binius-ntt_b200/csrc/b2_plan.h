@@ -113,6 +113,8 @@ inline int plan_build(HostPlan& hp, int field_bits, int layout, int log_h, int l
 	const int nbf = hp.nb - hp.batch_bits;  // butterfly line bits
 	hp.passes.clear();
 	hp.tiny = nbf < 1;
+	const bool use_upper6 = use_upper != 3;  // 3: as 2 but without the 6-bit passes (A/B runs)
+	if (use_upper == 3) use_upper = 2;
 	if (!hp.tiny && use_upper == 2 && nbf >= 9 - hp.batch_bits) {
 		// lowest pass: 512-line tiles (kind 2) = 9 - batch_bits butterfly line bits; above it upper passes of 4
 		// (or 2) line bits; an odd remainder goes to one bundle pass of 3 (or 1) bits at the top
@@ -122,6 +124,17 @@ inline int plan_build(HostPlan& hp, int field_bits, int layout, int log_h, int l
 			const int kt = left >= 3 ? 3 : 1;
 			q -= kt, left -= kt;
 			hp.passes.push_back(PassDesc{q, kt, 0, 0});
+		}
+		// from the top: 6 line bits per pass while none of their stages has a full GF(2^32) twiddle (class 5 needs the
+		// 81-group leaf table, which only fits for 15 twiddles), then 4, with one pass of 2 when the count asks for it
+		auto cheap6 = [&](int qtop) {  // stages of the line bits [qtop - 6, qtop)
+			for (int bq = qtop - 6; bq < qtop; bq++)
+				if (hp.cls[hp.n_inline + bq - hp.batch_bits] == 5) return false;
+			return true;
+		};
+		while (use_upper6 && left >= 6 && (left - 6) % 2 == 0 && cheap6(q)) {
+			q -= 6, left -= 6;
+			hp.passes.push_back(PassDesc{q, 6, 0, 1});
 		}
 		if (left & 3) {
 			q -= 2, left -= 2;
@@ -222,12 +235,17 @@ inline void plan_fill_upper(const HostPlan& hp, UpperParams& U, int n, const uin
 	U.coset0 = single ? coset : 0;
 	U.consts = consts;
 	U.log_h = hp.log_h, U.nb = hp.nb, U.q0 = pd.q0, U.k = pd.k;
+	U.ls = pd.k == 6 ? 3 : 5;
 	U.stage0 = hp.n_inline + pd.q0 - hp.batch_bits;
 	U.src_sliced = (hp.sliced_io || !first_pass) ? 1 : 0;
 	U.dst_sliced = (hp.sliced_io || !last_pass) ? 1 : 0;
 	U.inverse = inverse ? 1 : 0;
-	U.n_groups = (uint64_t)rows << (hp.nb - pd.k - 5);
-	for (int i = 0; i < pd.k; i++) U.cls[i] = hp.cls[U.stage0 + i];
+	U.n_groups = (uint64_t)rows << (hp.nb - pd.k - U.ls);
+	U.lpitch = 27;
+	for (int i = 0; i < pd.k; i++) {
+		U.cls[i] = hp.cls[U.stage0 + i];
+		if (U.cls[i] == 5) U.lpitch = 81;
+	}
 }
 
 // Parameters of the lowest pass (kind 2).
@@ -236,7 +254,7 @@ inline void plan_fill_bottom(const HostPlan& hp, BottomParams& B, int n, const u
 	memset(&B, 0, sizeof B);
 	plan_fill_upper(hp, B.up, n, src, dst, consts, inverse, coset, one_coset);
 	UpperParams& U = B.up;
-	U.q0 = 5, U.k = 4;
+	U.q0 = 5, U.k = 4, U.ls = 5, U.lpitch = 81;
 	U.stage0 = hp.n_inline + 5 - hp.batch_bits;
 	const bool single = inverse || one_coset;
 	const int rows = single ? hp.batch : hp.batch << hp.log_rate;

@@ -26,6 +26,7 @@ namespace b2 {
 constexpr int kUpperWarps = 4;        // warps per CTA
 constexpr int kLeafPitch = 81 * 4;    // words per twiddle in the leaf-mask table (class 5: 81 GF(4) groups x {m0, m1, m0^m1, pad})
 constexpr int kUpperMaxTw = 15;       // twiddles of a k = 4 group: 8 + 4 + 2 + 1
+constexpr int kLeafTableWords = 63 * 27 * 4;  // the larger of 15 x 81 (k = 4, class 5) and 63 x 27 (k = 6, classes <= 4) leaf groups
 
 struct alignas(16) Mask4 {
 	uint32_t x, y, z, w;
@@ -128,30 +129,32 @@ struct UpperParams {
 	const uint32_t* consts;  // [32][kConstPitch] normalised subspace constants (additive_ntt.cuh:273-309)
 	int log_h;             // of the whole transform (twiddle index shift)
 	int nb;                // line bits per row
-	int q0, k;             // this pass owns line bits [q0, q0+k), q0 >= 5, k = 2 or 4
+	int q0, k;             // this pass owns line bits [q0, q0+k), q0 >= 5, k = 2, 4 or 6
+	int ls;                // log2 of the lines per super-line: 5 (k = 2, 4), 3 (k = 6)
+	int lpitch;            // leaf groups per twiddle in the table: 81, or 27 when no layer of the pass has class 5
 	int stage0;            // butterfly stage of local bit 0
 	int src_sliced, dst_sliced;  // lines are bundles already / stay bundles (no 32x32 transpose)
 	int inverse;
 	uint64_t n_groups;     // rows << (nb - k - 5)
-	uint8_t cls[4];        // twiddle class of local bit i (0, 2..5)
+	uint8_t cls[8];        // twiddle class of local bit i (0, 2..5)
 };
 
 constexpr int kUSlotWords = 36;  // padded line slot in the exchange buffer (as b2_pass.cuh)
 B2_HD size_t upper_smem_words(int k) {
 	(void)k;
-	return (size_t)kUpperMaxTw * kLeafPitch + 16 + 1024 + (size_t)16 * 32 * kUSlotWords;
+	return (size_t)kLeafTableWords + 64 + 1024 + (size_t)512 * kUSlotWords;
 }
 struct UpperSmem {
-	Mask4* leaves;     // [kUpperMaxTw][81]
-	uint32_t* tw;      // [16] twiddle words
+	Mask4* leaves;     // [2^k - 1][lpitch]
+	uint32_t* tw;      // [64] twiddle words
 	uint32_t* consts;  // [32][32] copy of the subspace constants
-	uint32_t* slots;   // [16 super-lines][32 lanes][kUSlotWords]; k = 2: 4 super-lines per warp
+	uint32_t* slots;   // [512 lines][kUSlotWords]: super-line x, line l at (x << ls) + l; k = 2: 4 super-lines per warp
 };
 B2_HD UpperSmem upper_smem_view(uint32_t* base) {
 	UpperSmem sm;
 	sm.leaves = reinterpret_cast<Mask4*>(base);
-	sm.tw = base + kUpperMaxTw * kLeafPitch;
-	sm.consts = sm.tw + 16;
+	sm.tw = base + kLeafTableWords;
+	sm.consts = sm.tw + 64;
 	sm.slots = sm.consts + 1024;
 	return sm;
 }
@@ -162,15 +165,15 @@ struct UGroup {
 };
 B2_HD UGroup upper_group(const UpperParams& P, uint64_t g) {
 	UGroup c;
-	const int gb = P.nb - P.k - 5;  // group bits per row
+	const int gb = P.nb - P.k - P.ls;  // group bits per row
 	c.row = (uint32_t)(g >> gb);
 	const uint64_t rem = g & ((uint64_t(1) << gb) - 1);
-	c.lo_hi = rem & ((uint64_t(1) << (P.q0 - 5)) - 1);
-	c.hi = rem >> (P.q0 - 5);
+	c.lo_hi = rem & ((uint64_t(1) << (P.q0 - P.ls)) - 1);
+	c.hi = rem >> (P.q0 - P.ls);
 	return c;
 }
 B2_HD uint64_t upper_line(const UpperParams& P, const UGroup& c, int x, int lane) {
-	return (c.hi << (P.q0 + P.k)) | ((uint64_t)x << P.q0) | (c.lo_hi << 5) | (uint64_t)lane;
+	return (c.hi << (P.q0 + P.k)) | ((uint64_t)x << P.q0) | (c.lo_hi << P.ls) | (uint64_t)lane;
 }
 // table index of the twiddle of layer i for the super-line x (depends on x >> (i+1))
 B2_HD int upper_tw_index(int k, int i, int x) { return (1 << (k - 1 - i)) - 1 + (x >> (i + 1)); }
@@ -189,15 +192,16 @@ B2_HD void upper_twiddles(const UpperParams& P, UpperSmem& sm, const UGroup& c, 
 		if ((ind >> b) & 1) w ^= t[b];
 	sm.tw[tid] = w;
 }
-// leaf masks of every twiddle: item = twiddle * 81 + group, strided over nthreads
+// leaf masks of every twiddle: item = twiddle * lpitch + group, strided over nthreads
 B2_HD void upper_leaves(const UpperParams& P, UpperSmem& sm, int tid, int nthreads) {
-	const int ntw = (1 << P.k) - 1;
-	for (int item = tid; item < ntw * 81; item += nthreads) {
-		const int tw = (item * 1619) >> 17, g = item - tw * 81;  // item / 81 for item < 1300
+	const int ntw = (1 << P.k) - 1, lp = P.lpitch;
+	for (int item = tid; item < ntw * lp; item += nthreads) {
+		const int tw = lp == 81 ? (item * 1619) >> 17 : (item * 607) >> 14;  // item / 81 (item < 1300), item / 27 (item < 1800)
+		const int g = item - tw * lp;
 		int lg = 0;
 		while ((tw + 1) >> (lg + 1)) lg++;
 		const int hw = P.cls[P.k - 1 - lg];
-		if (g < leaf_groups(hw)) sm.leaves[tw * 81 + g] = leaf_group(sm.tw[tw], hw, g);
+		if (g < leaf_groups(hw)) sm.leaves[tw * lp + g] = leaf_group(sm.tw[tw], hw, g);
 	}
 }
 
@@ -230,7 +234,7 @@ B2_HD void line_store(uint32_t* p, const uint32_t* w) {
 //   last : the slots are copied to the pass output afterwards (transpose back for a compact output)
 template <bool INV>
 B2_HD void upper_pair(const UpperParams& P, const UpperSmem& sm, int lane, int xbase, int xshift, int slot_off, int b1, bool first, bool last) {
-	const int k = P.k;
+	const int k = P.k, ls = P.ls, l = lane & ((1 << ls) - 1);  // the lane's line inside every super-line it meets
 #pragma unroll 1
 	for (int step = 0; step < 2; step++) {
 		const bool top = INV ? step == 1 : step == 0;  // which of the two layers
@@ -240,8 +244,8 @@ B2_HD void upper_pair(const UpperParams& P, const UpperSmem& sm, int lane, int x
 		for (int j = 0; j < 2; j++) {
 			const int au = top ? j : 2 * j, av = top ? j + 2 : 2 * j + 1;
 			const int xu = xbase | (au << xshift), xv = xbase | (av << xshift);
-			uint32_t* su = sm.slots + ((size_t)(slot_off + xu) * 32 + lane) * kUSlotWords;
-			uint32_t* sv = sm.slots + ((size_t)(slot_off + xv) * 32 + lane) * kUSlotWords;
+			uint32_t* su = sm.slots + ((size_t)((slot_off + xu) << ls) + l) * kUSlotWords;
+			uint32_t* sv = sm.slots + ((size_t)((slot_off + xv) << ls) + l) * kUSlotWords;
 			uint32_t U[32], V[32];
 			line_load(su, U);
 			line_load(sv, V);
@@ -249,7 +253,7 @@ B2_HD void upper_pair(const UpperParams& P, const UpperSmem& sm, int lane, int x
 				transpose32(U);
 				transpose32(V);
 			}
-			butterfly_const_dispatch<INV>(cls, U, V, sm.leaves + 81 * upper_tw_index(k, bit, xu));
+			butterfly_const_dispatch<INV>(cls, U, V, sm.leaves + P.lpitch * upper_tw_index(k, bit, xu));
 			if (last && step == 1 && !P.dst_sliced) {
 				transpose32(U);
 				transpose32(V);
@@ -261,26 +265,30 @@ B2_HD void upper_pair(const UpperParams& P, const UpperSmem& sm, int lane, int x
 }
 
 // ---- coalesced copies of super-lines: global <-> slots, 16-byte chunks ---------------------------------
-// Copies the nsl super-lines x = x0, x0 + xstep, ... of the group between global memory and the slots slot_off + x.
-// A thread keeps its 16-byte piece (tid & 7) and walks lines tid >> 3, + nthreads / 8, ... of every super-line, so all
-// addresses advance by constant strides (nthreads = 32: one warp moves its own quad; 128: the CTA moves the group).
+// One warp copies the super-lines x = x0 + i1 * s1 + i2 * s2 (i1 < n1, i2 < n2) of the group between global memory and
+// the slots (slot_off + x).  A super-line is 2^ls lines = 2^(ls+3) 16-byte chunks, contiguous in global memory; the
+// warp moves 32 consecutive chunks (512 bytes) per step.
 template <bool STORE>
-B2_HD void upper_copy(const UpperParams& P, const UpperSmem& sm, const UGroup& c, int slot_off, int x0, int xstep, int nsl, int tid, int nthreads) {
-	const int piece = tid & 7, ln0 = tid >> 3, dl = nthreads >> 3, per = 256 / nthreads;
-	const uint64_t g0 = upper_line(P, c, x0, ln0) * 32 + piece * 4, gx = ((uint64_t)32 << P.q0) * xstep;
-	const uint32_t* gs = P.src + (uint64_t)(c.row >> P.src_row_shift) * P.src_row_words + g0;
-	uint32_t* gd = P.dst + (uint64_t)c.row * P.dst_row_words + g0;
-	uint32_t* s = sm.slots + ((size_t)(slot_off + x0) * 32 + ln0) * kUSlotWords + piece * 4;
+B2_HD void upper_copy(const UpperParams& P, const UpperSmem& sm, const UGroup& c, int slot_off, int x0, int s1, int n1, int s2, int n2, int lane) {
+	const int ls = P.ls, steps = 1 << (ls - 2);  // steps per super-line
+	const int piece = lane & 7, l0 = lane >> 3;
+	const uint32_t* srow = P.src + (uint64_t)(c.row >> P.src_row_shift) * P.src_row_words;
+	uint32_t* drow = P.dst + (uint64_t)c.row * P.dst_row_words;
+#pragma unroll 1
+	for (int i2 = 0; i2 < n2; i2++) {
+#pragma unroll 1
+		for (int i1 = 0; i1 < n1; i1++) {
+			const int x = x0 + i1 * s1 + i2 * s2;
+			const uint64_t g = upper_line(P, c, x, l0) * 32 + piece * 4;
+			uint32_t* s = sm.slots + ((size_t)((slot_off + x) << ls) + l0) * kUSlotWords + piece * 4;
 #pragma unroll 2
-	for (int x = 0; x < nsl; x++) {
-#pragma unroll 2
-		for (int j = 0; j < per; j++) {
-			if (STORE)
-				copy16_s2g(gd + (size_t)j * dl * 32, s + (size_t)j * dl * kUSlotWords);
-			else
-				copy16_g2s(s + (size_t)j * dl * kUSlotWords, gs + (size_t)j * dl * 32);
+			for (int st = 0; st < steps; st++) {
+				if (STORE)
+					copy16_s2g(drow + g + (size_t)st * 128, s + (size_t)st * 4 * kUSlotWords);
+				else
+					copy16_g2s(s + (size_t)st * 4 * kUSlotWords, srow + g + (size_t)st * 128);
+			}
 		}
-		gs += gx, gd += gx, s += (size_t)xstep * 32 * kUSlotWords;
 	}
 }
 

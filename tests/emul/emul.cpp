@@ -39,22 +39,23 @@ static void run_upper(const UpperParams& P) {
 		const UGroup c = upper_group(P, grp);
 		for (int t = 0; t < T; t++) upper_twiddles(P, sm, c, t, P.consts);
 		for (int t = 0; t < T; t++) upper_leaves(P, sm, t, T);
-		if (P.k == 4) {
-			for (int t = 0; t < T; t++) upper_copy<false>(P, sm, c, 0, 0, 1, 16, t, T);
-			for (int t = 0; t < T; t++) {
-				if (!INV) upper_pair<INV>(P, sm, t & 31, t >> 5, 2, 0, 3, true, false);
-				else upper_pair<INV>(P, sm, t & 31, (t >> 5) << 2, 0, 0, 1, true, false);
+		if (P.k >= 4) {
+			const int k = P.k, ls = P.ls, upw = 1 << (k - 4), nph = k >> 1;
+			for (int lane = 0; lane < 32; lane++) upper_copy<false>(P, sm, c, 0, 0, 1, 1 << k, 0, 1, lane);
+			for (int e = 0; e < nph; e++) {
+				const int j = INV ? nph - 1 - e : e, b1 = k - 1 - 2 * j, b0 = b1 - 1;
+				for (int t = 0; t < T; t++) {
+					const int warp = t >> 5, lane = t & 31, u = warp * upw + (lane >> ls);
+					const int xbase = ((u >> b0) << (b1 + 1)) | (u & ((1 << b0) - 1));
+					upper_pair<INV>(P, sm, lane, xbase, b0, 0, b1, e == 0, e == nph - 1);
+				}
 			}
-			for (int t = 0; t < T; t++) {
-				if (!INV) upper_pair<INV>(P, sm, t & 31, (t >> 5) << 2, 0, 0, 1, false, true);
-				else upper_pair<INV>(P, sm, t & 31, t >> 5, 2, 0, 3, false, true);
-			}
-			for (int t = 0; t < T; t++) upper_copy<true>(P, sm, c, 0, 0, 1, 16, t, T);
+			for (int lane = 0; lane < 32; lane++) upper_copy<true>(P, sm, c, 0, 0, 1, 1 << k, 0, 1, lane);
 		} else {
 			const int w = (int)(grp & 3);  // any warp slot
-			for (int t = 0; t < 32; t++) upper_copy<false>(P, sm, c, w * 4, 0, 1, 4, t, 32);
+			for (int t = 0; t < 32; t++) upper_copy<false>(P, sm, c, w * 4, 0, 1, 4, 0, 1, t);
 			for (int t = 0; t < 32; t++) upper_pair<INV>(P, sm, t, 0, 0, w * 4, 1, true, true);
-			for (int t = 0; t < 32; t++) upper_copy<true>(P, sm, c, w * 4, 0, 1, 4, t, 32);
+			for (int t = 0; t < 32; t++) upper_copy<true>(P, sm, c, w * 4, 0, 1, 4, 0, 1, t);
 		}
 	}
 }
@@ -70,7 +71,7 @@ static void run_bottom(const BottomParams& B) {
 	for (uint64_t grp = 0; grp < P.n_groups; grp++) {
 		const UGroup c = upper_group(P, grp);
 		for (int t = 0; t < T; t++) upper_twiddles(P, bs.us, c, t, P.consts), bottom_tile_tables(B, bs, c, t - 16, P.consts);
-		for (int t = 0; t < T; t++) upper_copy<false>(P, bs.us, c, 0, 0, 1, 16, t, T);
+		for (int lane = 0; lane < 32; lane++) upper_copy<false>(P, bs.us, c, 0, 0, 1, 16, 0, 1, lane);
 		for (int t = 0; t < T; t++) upper_leaves(P, bs.us, t, T);
 		if (!INV) {
 			for (int t = 0; t < T; t++) upper_pair<false>(P, bs.us, t & 31, t >> 5, 2, 0, 3, true, false);
@@ -83,7 +84,7 @@ static void run_bottom(const BottomParams& B) {
 			for (int t = 0; t < T; t++) upper_pair<true>(P, bs.us, t & 31, (t >> 5) << 2, 0, 0, 1, false, false);
 			for (int t = 0; t < T; t++) upper_pair<true>(P, bs.us, t & 31, t >> 5, 2, 0, 3, false, true);
 		}
-		for (int t = 0; t < T; t++) upper_copy<true>(P, bs.us, c, 0, 0, 1, 16, t, T);
+		for (int lane = 0; lane < 32; lane++) upper_copy<true>(P, bs.us, c, 0, 0, 1, 16, 0, 1, lane);
 	}
 }
 

@@ -136,7 +136,8 @@ def emul():
 @pytest.mark.parametrize("field_bits,layout,log_h,log_rate", [
     (32, 0, 6, 0), (32, 0, 12, 0), (32, 0, 15, 2), (128, 0, 4, 0), (128, 0, 10, 0), (128, 0, 13, 1),
     (32, 1, 9, 0), (128, 1, 8, 1), (32, 0, 16, 0),
-    (128, 0, 15, 1), (32, 1, 17, 0), (128, 1, 16, 0), (128, 0, 17, 0), (128, 0, 12, 0), (32, 0, 14, 1)])  # the last six reach the tile pass and the upper passes
+    (128, 0, 15, 1), (32, 1, 17, 0), (128, 1, 16, 0), (128, 0, 17, 0), (128, 0, 12, 0), (32, 0, 14, 1),
+    (32, 0, 20, 0), (128, 0, 18, 1)])  # 6-bit upper passes on 8-line super-lines  # the last six reach the tile pass and the upper passes
 def test_emulated_kernels_match_oracle(oracle, emul, field_bits, layout, log_h, log_rate):
     limbs = field_bits // 32
     x = _rand((1 << log_h) * limbs, 17 * log_h + log_rate)
