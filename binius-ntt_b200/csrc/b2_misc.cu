@@ -181,21 +181,28 @@ __device__ __forceinline__ void sliced64_mul_from(const uint32_t* a0p, const uin
 	}
 }
 
-// 32 blocks (16 KB per operand) per CTA iteration: operands come in by coalesced cp.async into padded rows (pitch 132
-// words: a quarter warp reading 16 bytes of 8 different rows hits 8 different bank groups), the three GF(2^64)
-// sub-products of a block go to three threads, are combined through shared memory, and the result rows leave by
-// coalesced 16-byte stores.
-constexpr int kMulPitch = 132;
-__global__ void __launch_bounds__(96) mul_sliced128_kernel(const uint32_t* __restrict__ a, const uint32_t* __restrict__ b, uint32_t* __restrict__ o, uint64_t n_blocks) {
-	// 96 threads = 32 blocks x 3 sub-products; thread (blk, q): q = threadIdx.x / 32
+// bit-sliced GF(2^128), 32 blocks (16 KB per operand) per CTA iteration.  Two Karatsuba levels above GF(2^32) give
+// nine GF(2^32) products per block: warp j of the 9 warps computes product j for the 32 blocks (lane = block), so a
+// thread holds one 32-word operand pair and its product.  Operands arrive by coalesced cp.async into padded rows
+// (pitch 132 words: conflict-free 16-byte reads of 8 different rows), the products are combined through shared
+// memory in two linear steps and the result rows leave by coalesced 16-byte stores.
+//   j = 3u + v:  u = 0: A0 = (a0, a1), 1: A1 = (a2, a3), 2: A0 + A1;  v = 0: low limb, 1: high limb, 2: their sum
+//   Z_u = (P_3u + P_3u+1,  P_3u+2 + P_3u + P_3u+1 + alpha5 * P_3u+1)           (GF(2^64) products)
+//   out = (Z_0 + Z_1,  Z_2 + Z_0 + Z_1 + alpha6 * Z_1),  alpha6 * (lo, hi) = (hi, lo + alpha5 * hi)
+constexpr int kMulPitch = 132, kProdPitch = 33;
+#ifndef B2_MUL128_CTAS
+#define B2_MUL128_CTAS 2  // 96 registers per thread (a few spilled words), two CTAs = 18 warps per SM: 9.1 ms vs 11.7 ms at one CTA
+#endif
+__global__ void __launch_bounds__(288, B2_MUL128_CTAS) mul_sliced128_kernel(const uint32_t* __restrict__ a, const uint32_t* __restrict__ b, uint32_t* __restrict__ o, uint64_t n_blocks) {
 	extern __shared__ __align__(16) uint32_t msm[];
-	uint32_t* sa = msm;                       // [32][132] operand a, later the result rows
-	uint32_t* sb = msm + 32 * kMulPitch;      // [32][132] operand b
-	uint32_t* sz = sb + 32 * kMulPitch;       // [3][32][65] sub-products
-	const int q = threadIdx.x >> 5, lb = threadIdx.x & 31;
+	uint32_t* sa = msm;                        // [32][132] operand a, later the result rows
+	uint32_t* sb = msm + 32 * kMulPitch;       // [32][132] operand b
+	uint32_t* sp = sb + 32 * kMulPitch;        // [9][32][33] products P_j
+	uint32_t* sz = sp + 9 * 32 * kProdPitch;   // [6][32][33] Z_u low / high halves
+	const int j = threadIdx.x >> 5, lb = threadIdx.x & 31, u = j / 3, v = j - 3 * u;
 	for (uint64_t g0 = (uint64_t)blockIdx.x * 32; g0 < n_blocks; g0 += (uint64_t)gridDim.x * 32) {
 		const int nact = n_blocks - g0 < 32 ? (int)(n_blocks - g0) : 32;
-		for (int ch = threadIdx.x; ch < nact * 32; ch += 96) {  // 16-byte chunks: 32 per block row
+		for (int ch = threadIdx.x; ch < nact * 32; ch += 288) {  // 16-byte chunks: 32 per block row
 			const int row = ch >> 5, c4 = (ch & 31) * 4;
 			const unsigned da = (unsigned)__cvta_generic_to_shared(sa + row * kMulPitch + c4), db = (unsigned)__cvta_generic_to_shared(sb + row * kMulPitch + c4);
 			asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(da), "l"(a + (g0 + row) * 128 + c4) : "memory");
@@ -205,37 +212,80 @@ __global__ void __launch_bounds__(96) mul_sliced128_kernel(const uint32_t* __res
 		__syncthreads();
 		const bool act = lb < nact;
 		if (act) {
-			uint32_t r[64];
+			// operand limbs of product j: limbs {l0} (+ {l0 + 1} when v = 2), the same from the other half when u = 2
+			uint32_t x[32], y[32], t[32];
 			const uint32_t *pa = sa + lb * kMulPitch, *pb = sb + lb * kMulPitch;
-			if (q == 0) sliced64_mul_from(pa, pa, pb, pb, false, 0, r);        // Z0 = A0*B0
-			else if (q == 1) sliced64_mul_from(pa, pa, pb, pb, false, 2, r);   // Z2 = A1*B1
-			else sliced64_mul_from(pa, pa + 64, pb, pb + 64, true, 0, r);      // ZZ = (A0+A1)*(B0+B1)
+			const int base = u == 1 ? 2 : 0, l0 = base + (v == 1 ? 1 : 0);
+			load32(pa + 32 * l0, x), load32(pb + 32 * l0, y);
+			if (v == 2) {
+				load32(pa + 32 * (l0 + 1), t);
 #pragma unroll
-			for (int i = 0; i < 64; i++) sz[(q * 32 + lb) * 65 + i] = r[i];
+				for (int i = 0; i < 32; i++) x[i] ^= t[i];
+				load32(pb + 32 * (l0 + 1), t);
+#pragma unroll
+				for (int i = 0; i < 32; i++) y[i] ^= t[i];
+			}
+			if (u == 2) {
+				load32(pa + 32 * (l0 + 2), t);
+#pragma unroll
+				for (int i = 0; i < 32; i++) x[i] ^= t[i];
+				load32(pb + 32 * (l0 + 2), t);
+#pragma unroll
+				for (int i = 0; i < 32; i++) y[i] ^= t[i];
+				if (v == 2) {
+					load32(pa + 32 * (l0 + 3), t);
+#pragma unroll
+					for (int i = 0; i < 32; i++) x[i] ^= t[i];
+					load32(pb + 32 * (l0 + 3), t);
+#pragma unroll
+					for (int i = 0; i < 32; i++) y[i] ^= t[i];
+				}
+			}
+			Sliced<5>::mul(x, y, t);
+#pragma unroll
+			for (int i = 0; i < 32; i++) sp[(j * 32 + lb) * kProdPitch + i] = t[i];
 		}
 		__syncthreads();
-		if (act) {
-			// lo = Z0 + Z2 ; hi = ZZ + Z0 + Z2 + alpha6 * Z2 ; result rows replace operand a
-			const uint32_t *z0 = sz + lb * 65, *z2p = sz + (32 + lb) * 65, *zz = sz + (64 + lb) * 65;
-			uint32_t* po = sa + lb * kMulPitch;
-			if (q == 0) {
-				for (int i = 0; i < 64; i++) po[i] = z0[i] ^ z2p[i];
-			} else if (q == 1) {
-				uint32_t z2[64], az[64];
-				for (int i = 0; i < 64; i++) z2[i] = z2p[i];
-				Sliced<6>::mul_alpha(z2, az);
-				for (int i = 0; i < 64; i++) po[64 + i] = zz[i] ^ z0[i] ^ z2[i] ^ az[i];
+		if (act && j < 6) {  // Z_u halves: warp 2u -> low, warp 2u + 1 -> high
+			const int uu = j >> 1;
+			const uint32_t *p0 = sp + ((3 * uu) * 32 + lb) * kProdPitch, *p1 = p0 + 32 * kProdPitch, *p2 = p1 + 32 * kProdPitch;
+			uint32_t* z = sz + (j * 32 + lb) * kProdPitch;
+			if (!(j & 1)) {
+				for (int i = 0; i < 32; i++) z[i] = p0[i] ^ p1[i];
+			} else {
+				uint32_t q[32], aq[32];
+				for (int i = 0; i < 32; i++) q[i] = p1[i];
+				Sliced<5>::mul_alpha(q, aq);
+				for (int i = 0; i < 32; i++) z[i] = p2[i] ^ p0[i] ^ q[i] ^ aq[i];
 			}
 		}
 		__syncthreads();
-		for (int ch = threadIdx.x; ch < nact * 32; ch += 96) {
+		if (act && j < 4) {  // result limb j of the block, into the row that held operand a
+			const uint32_t *z0l = sz + lb * kProdPitch, *z0h = z0l + 32 * kProdPitch, *z1l = z0h + 32 * kProdPitch, *z1h = z1l + 32 * kProdPitch,
+			               *z2l = z1h + 32 * kProdPitch, *z2h = z2l + 32 * kProdPitch;
+			uint32_t* po = sa + lb * kMulPitch + 32 * j;
+			if (j == 0) {
+				for (int i = 0; i < 32; i++) po[i] = z0l[i] ^ z1l[i];
+			} else if (j == 1) {
+				for (int i = 0; i < 32; i++) po[i] = z0h[i] ^ z1h[i];
+			} else if (j == 2) {
+				for (int i = 0; i < 32; i++) po[i] = z2l[i] ^ z0l[i] ^ z1l[i] ^ z1h[i];
+			} else {
+				uint32_t q[32], aq[32];
+				for (int i = 0; i < 32; i++) q[i] = z1h[i];
+				Sliced<5>::mul_alpha(q, aq);
+				for (int i = 0; i < 32; i++) po[i] = z2h[i] ^ z0h[i] ^ q[i] ^ z1l[i] ^ aq[i];
+			}
+		}
+		__syncthreads();
+		for (int ch = threadIdx.x; ch < nact * 32; ch += 288) {
 			const int row = ch >> 5, c4 = (ch & 31) * 4;
 			*reinterpret_cast<uint4*>(o + (g0 + row) * 128 + c4) = *reinterpret_cast<const uint4*>(sa + row * kMulPitch + c4);
 		}
 		__syncthreads();
 	}
 }
-constexpr size_t kMulSmemBytes = (2 * 32 * kMulPitch + 3 * 32 * 65) * sizeof(uint32_t);
+constexpr size_t kMulSmemBytes = (2 * 32 * kMulPitch + 15 * 32 * kProdPitch) * sizeof(uint32_t);
 
 int launch_mul(int field_bits, int layout, const uint32_t* a, const uint32_t* b, uint32_t* o, uint64_t n, cudaStream_t stream) {
 	if (n == 0) return 0;
@@ -263,7 +313,7 @@ int launch_mul(int field_bits, int layout, const uint32_t* a, const uint32_t* b,
 			unsigned blocks = (unsigned)((nb + 31) / 32);
 			if (blocks > cap) blocks = cap;
 			cudaFuncSetAttribute(mul_sliced128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMulSmemBytes);
-			mul_sliced128_kernel<<<blocks, 96, kMulSmemBytes, stream>>>(a, b, o, nb);
+			mul_sliced128_kernel<<<blocks, 288, kMulSmemBytes, stream>>>(a, b, o, nb);
 		} else
 			return -1;
 	}
