@@ -102,17 +102,6 @@ __global__ void mul_compact_kernel(const uint32_t* __restrict__ a, const uint32_
 		o[g] = (uint32_t)Tower<H>::mul(a[g], b[g]);
 }
 
-__global__ void mul_compact128_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, uint4* __restrict__ o, uint64_t n) {
-	for (uint64_t g = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; g < n; g += (uint64_t)gridDim.x * blockDim.x) {
-		const uint4 x = a[g], y = b[g];
-		gf128 p, q;
-		p.w[0] = x.x, p.w[1] = x.y, p.w[2] = x.z, p.w[3] = x.w;
-		q.w[0] = y.x, q.w[1] = y.y, q.w[2] = y.z, q.w[3] = y.w;
-		const gf128 z = gf128_mul(p, q);
-		o[g] = make_uint4(z.w[0], z.w[1], z.w[2], z.w[3]);
-	}
-}
-
 // bit-sliced GF(2^32): one thread per block of 32 products, everything in registers
 __global__ void __launch_bounds__(128) mul_sliced32_kernel(const uint32_t* __restrict__ a, const uint32_t* __restrict__ b, uint32_t* __restrict__ o, uint64_t n_blocks) {
 	for (uint64_t g = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; g < n_blocks; g += (uint64_t)gridDim.x * blockDim.x) {
@@ -193,7 +182,12 @@ constexpr int kMulPitch = 132, kProdPitch = 33;
 #ifndef B2_MUL128_CTAS
 #define B2_MUL128_CTAS 2  // 96 registers per thread (a few spilled words), two CTAs = 18 warps per SM: 9.1 ms vs 11.7 ms at one CTA
 #endif
-__global__ void __launch_bounds__(288, B2_MUL128_CTAS) mul_sliced128_kernel(const uint32_t* __restrict__ a, const uint32_t* __restrict__ b, uint32_t* __restrict__ o, uint64_t n_blocks) {
+// COMPACT = true: the operands are compact GF(2^128) elements (multiply<7>, finite_fields/binary_tower.cuh): a block row is
+// 32 elements x 4 limbs; warps 0..7 bit-slice the staged rows in place (lane = 4 * block + limb: conflict-free gathers),
+// the product runs bit-sliced as above and warps 0..3 transpose the result rows back before the store.  n_chunks = number
+// of valid 16-byte chunks (= elements when compact), so a ragged last block is neither read nor written past its end.
+template <bool COMPACT>
+__global__ void __launch_bounds__(288, B2_MUL128_CTAS) mul_sliced128_kernel(const uint32_t* __restrict__ a, const uint32_t* __restrict__ b, uint32_t* __restrict__ o, uint64_t n_blocks, uint64_t n_chunks) {
 	extern __shared__ __align__(16) uint32_t msm[];
 	uint32_t* sa = msm;                        // [32][132] operand a, later the result rows
 	uint32_t* sb = msm + 32 * kMulPitch;       // [32][132] operand b
@@ -204,12 +198,27 @@ __global__ void __launch_bounds__(288, B2_MUL128_CTAS) mul_sliced128_kernel(cons
 		const int nact = n_blocks - g0 < 32 ? (int)(n_blocks - g0) : 32;
 		for (int ch = threadIdx.x; ch < nact * 32; ch += 288) {  // 16-byte chunks: 32 per block row
 			const int row = ch >> 5, c4 = (ch & 31) * 4;
+			if ((g0 + row) * 32 + (ch & 31) >= n_chunks) continue;
 			const unsigned da = (unsigned)__cvta_generic_to_shared(sa + row * kMulPitch + c4), db = (unsigned)__cvta_generic_to_shared(sb + row * kMulPitch + c4);
 			asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(da), "l"(a + (g0 + row) * 128 + c4) : "memory");
 			asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(db), "l"(b + (g0 + row) * 128 + c4) : "memory");
 		}
 		asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
 		__syncthreads();
+		if (COMPACT) {
+			if (j < 8) {
+				uint32_t r[32];
+				uint32_t* row = (j < 4 ? sa : sb) + (8 * (j & 3) + (lb >> 2)) * kMulPitch;
+				const int k = lb & 3;
+#pragma unroll
+				for (int e = 0; e < 32; e++) r[e] = row[4 * e + k];
+				transpose32(r);
+				__syncwarp();
+#pragma unroll
+				for (int i = 0; i < 32; i++) row[32 * k + i] = r[i];
+			}
+			__syncthreads();
+		}
 		const bool act = lb < nact;
 		if (act) {
 			// operand limbs of product j: limbs {l0} (+ {l0 + 1} when v = 2), the same from the other half when u = 2
@@ -278,8 +287,23 @@ __global__ void __launch_bounds__(288, B2_MUL128_CTAS) mul_sliced128_kernel(cons
 			}
 		}
 		__syncthreads();
+		if (COMPACT) {
+			if (j < 4) {
+				uint32_t r[32];
+				uint32_t* row = sa + (8 * j + (lb >> 2)) * kMulPitch;
+				const int k = lb & 3;
+#pragma unroll
+				for (int i = 0; i < 32; i++) r[i] = row[32 * k + i];
+				transpose32(r);
+				__syncwarp();
+#pragma unroll
+				for (int e = 0; e < 32; e++) row[4 * e + k] = r[e];
+			}
+			__syncthreads();
+		}
 		for (int ch = threadIdx.x; ch < nact * 32; ch += 288) {
 			const int row = ch >> 5, c4 = (ch & 31) * 4;
+			if ((g0 + row) * 32 + (ch & 31) >= n_chunks) continue;
 			*reinterpret_cast<uint4*>(o + (g0 + row) * 128 + c4) = *reinterpret_cast<const uint4*>(sa + row * kMulPitch + c4);
 		}
 		__syncthreads();
@@ -297,9 +321,14 @@ int launch_mul(int field_bits, int layout, const uint32_t* a, const uint32_t* b,
 			case 8: mul_compact_kernel<3><<<blocks, 256, 0, stream>>>(a, b, o, n); break;
 			case 16: mul_compact_kernel<4><<<blocks, 256, 0, stream>>>(a, b, o, n); break;
 			case 32: mul_compact_kernel<5><<<blocks, 256, 0, stream>>>(a, b, o, n); break;
-			case 128:
-				mul_compact128_kernel<<<blocks, 256, 0, stream>>>((const uint4*)a, (const uint4*)b, (uint4*)o, n);
+			case 128: {
+				const uint64_t nb = (n + 31) / 32;
+				blocks = (unsigned)((nb + 31) / 32);
+				if (blocks > cap) blocks = cap;
+				cudaFuncSetAttribute(mul_sliced128_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMulSmemBytes);
+				mul_sliced128_kernel<true><<<blocks, 288, kMulSmemBytes, stream>>>(a, b, o, nb, n);
 				break;
+			}
 			default: return -1;
 		}
 	} else {
@@ -312,8 +341,8 @@ int launch_mul(int field_bits, int layout, const uint32_t* a, const uint32_t* b,
 		} else if (field_bits == 128) {
 			unsigned blocks = (unsigned)((nb + 31) / 32);
 			if (blocks > cap) blocks = cap;
-			cudaFuncSetAttribute(mul_sliced128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMulSmemBytes);
-			mul_sliced128_kernel<<<blocks, 288, kMulSmemBytes, stream>>>(a, b, o, nb);
+			cudaFuncSetAttribute(mul_sliced128_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMulSmemBytes);
+			mul_sliced128_kernel<false><<<blocks, 288, kMulSmemBytes, stream>>>(a, b, o, nb, nb * 32);
 		} else
 			return -1;
 	}

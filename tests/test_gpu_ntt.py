@@ -127,6 +127,54 @@ def test_full_size_properties_gf128(b2, oracle, cuda):
     assert torch.equal(plan.exec_inverse(fa), a)
 
 
+def test_headline_size_properties_gf128(b2, oracle, cuda):
+    """BASELINE metric size, log_n = 28 GF(2^128) (4 GiB): limb-0 golden digest (ntt/tests/test_ntt.cu:52-124, F8),
+    linearity, inverse round trip."""
+    import torch
+
+    log_h = 28
+    n = 1 << log_h
+    g = torch.Generator(device=cuda).manual_seed(28)
+    a = torch.randint(-2**31, 2**31 - 1, (n * 4,), dtype=torch.int32, device=cuda, generator=g)
+    b = torch.randint(-2**31, 2**31 - 1, (n * 4,), dtype=torch.int32, device=cuda, generator=g)
+    a.view(-1, 4)[:, 0] = _dev(oracle.reference_input(log_h, 0), cuda)
+    plan = b2.Plan(128, log_h, 0)
+    fa = plan.exec(a.clone())
+    assert oracle.md5_hex(_host(fa.view(-1, 4)[:, 0].contiguous())) == oracle.golden_md5(0, log_h)
+    fab = plan.exec(a ^ b)
+    fab ^= fa
+    assert torch.equal(fab, plan.exec(b.clone()))
+    del fab, b
+    assert torch.equal(plan.exec_inverse(fa), a)
+    plan.close()
+
+
+def test_config2_compact_and_bitsliced_agree(b2, oracle, cuda):
+    """config 2: log_n = 24 GF(2^128), the bit-sliced image transforms to the bit-sliced image of the compact result"""
+    import torch
+
+    log_h = 24
+    x = torch.randint(-2**31, 2**31 - 1, ((1 << log_h) * 4,), dtype=torch.int32, device=cuda, generator=torch.Generator(device=cuda).manual_seed(24))
+    yc = b2.Plan(128, log_h, 0).exec(x.clone())
+    xs = x.clone()
+    b2.bitslice_(xs, 128)
+    ys = b2.Plan(128, log_h, 0, layout=b2.api.LAYOUT_BITSLICED).exec(xs)
+    b2.bitslice_(ys, 128, inverse=True)
+    assert torch.equal(ys, yc)
+
+
+def test_config3_rs_columns_golden(b2, oracle, cuda):
+    """config 3 shape (log_h = 20, log_rate = 2, GF(2^32)) on a batch of columns: every column carrying the reference
+    stream reproduces the reference digest 53e8a086... (ntt/tests/test_ntt.cu:112)"""
+    cols = 8
+    x = oracle.reference_input(20, 2)
+    plan = b2.Plan(32, 20, 2, batch=cols)
+    out = _host(plan.exec(_dev(np.tile(x, cols), cuda)))
+    for c in range(cols):
+        assert oracle.md5_hex(out[c << 22:(c + 1) << 22]) == oracle.golden_md5(2, 20) == "53e8a086be97f61f43930357442272cb"
+    plan.close()
+
+
 def test_error_paths(b2, cuda):
     with pytest.raises(b2.B2NTTError):
         b2.Plan(32, 0, 0)
