@@ -102,6 +102,50 @@ __global__ void mul_compact_kernel(const uint32_t* __restrict__ a, const uint32_
 		o[g] = (uint32_t)Tower<H>::mul(a[g], b[g]);
 }
 
+// compact GF(2^32) (multiply<5>, finite_fields/binary_tower.cuh): a warp stages 32 lines per operand through shared
+// memory (coalesced), each lane bit-slices its own line of 32 elements in registers, multiplies bit-sliced and
+// transposes the products back -- ~1.5k logic instructions per 32 products instead of one tower recursion per element.
+__global__ void __launch_bounds__(128) mul_compact32_kernel(const uint32_t* __restrict__ a, const uint32_t* __restrict__ b, uint32_t* __restrict__ o, uint64_t n) {
+	__shared__ uint32_t sm[4][32 * 33];
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	uint32_t* s = sm[warp];
+	const uint64_t n_groups = (n + 1023) / 1024;
+	for (uint64_t grp = (uint64_t)blockIdx.x * 4 + warp; grp < n_groups; grp += (uint64_t)gridDim.x * 4) {
+		const uint64_t base = grp * 1024;
+		uint32_t x[32], y[32], z[32];
+#pragma unroll
+		for (int i = 0; i < 32; i++) {
+			const uint64_t g = base + (uint64_t)i * 32 + lane;
+			s[i * 33 + lane] = g < n ? a[g] : 0u;
+		}
+		__syncwarp();
+#pragma unroll
+		for (int e = 0; e < 32; e++) x[e] = s[lane * 33 + e];
+		__syncwarp();
+#pragma unroll
+		for (int i = 0; i < 32; i++) {
+			const uint64_t g = base + (uint64_t)i * 32 + lane;
+			s[i * 33 + lane] = g < n ? b[g] : 0u;
+		}
+		__syncwarp();
+#pragma unroll
+		for (int e = 0; e < 32; e++) y[e] = s[lane * 33 + e];
+		__syncwarp();
+		transpose32(x), transpose32(y);
+		Sliced<5>::mul(x, y, z);
+		transpose32(z);
+#pragma unroll
+		for (int e = 0; e < 32; e++) s[lane * 33 + e] = z[e];
+		__syncwarp();
+#pragma unroll
+		for (int i = 0; i < 32; i++) {
+			const uint64_t g = base + (uint64_t)i * 32 + lane;
+			if (g < n) o[g] = s[i * 33 + lane];
+		}
+		__syncwarp();
+	}
+}
+
 // bit-sliced GF(2^32): one thread per block of 32 products, everything in registers
 __global__ void __launch_bounds__(128) mul_sliced32_kernel(const uint32_t* __restrict__ a, const uint32_t* __restrict__ b, uint32_t* __restrict__ o, uint64_t n_blocks) {
 	for (uint64_t g = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; g < n_blocks; g += (uint64_t)gridDim.x * blockDim.x) {
@@ -320,7 +364,11 @@ int launch_mul(int field_bits, int layout, const uint32_t* a, const uint32_t* b,
 		switch (field_bits) {
 			case 8: mul_compact_kernel<3><<<blocks, 256, 0, stream>>>(a, b, o, n); break;
 			case 16: mul_compact_kernel<4><<<blocks, 256, 0, stream>>>(a, b, o, n); break;
-			case 32: mul_compact_kernel<5><<<blocks, 256, 0, stream>>>(a, b, o, n); break;
+			case 32:
+				blocks = (unsigned)((n + 4095) / 4096);
+				if (blocks > cap) blocks = cap;
+				mul_compact32_kernel<<<blocks, 128, 0, stream>>>(a, b, o, n);
+				break;
 			case 128: {
 				const uint64_t nb = (n + 31) / 32;
 				blocks = (unsigned)((nb + 31) / 32);
