@@ -12,6 +12,7 @@ from .api import (  # noqa: F401
     DataOrder,
     NTTData,
     Plan,
+    Sumcheck,
     bitslice_,
     check_gpu_capabilities,
     lib,

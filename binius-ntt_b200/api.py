@@ -49,6 +49,15 @@ def lib():
         L.b2ntt_mul.argtypes = [i, i, vp, vp, vp, sz, vp]
         L.b2ntt_mul_repeat.argtypes = [i, vp, sz, i, vp]
         L.b2ntt_check_gpu_capabilities.argtypes = [i]
+        L.b2ntt_sumcheck_create.argtypes = [C.POINTER(vp), i, i, i]
+        L.b2ntt_sumcheck_destroy.argtypes = [vp]
+        L.b2ntt_sumcheck_load_host.argtypes = [vp, vp, i]
+        L.b2ntt_sumcheck_load_device.argtypes = [vp, vp, i]
+        L.b2ntt_sumcheck_round_messages.argtypes = [vp, vp, vp]
+        L.b2ntt_sumcheck_next_round.argtypes = [vp, vp]
+        L.b2ntt_sumcheck_round.argtypes = [vp]
+        L.b2ntt_sumcheck_launches.argtypes = [vp]
+        L.b2ntt_sumcheck_launches.restype = C.c_longlong
         L.b2ntt_strerror.argtypes = [i]
         L.b2ntt_strerror.restype = C.c_char_p
         L.b2ntt_last_cuda_error.restype = C.c_char_p
@@ -274,3 +283,68 @@ class AdditiveNTT:
         out.order = DataOrder.IN_ORDER
         self.plan.exec_host(inp.data, out.data)
         return True
+
+
+class Sumcheck:
+    """Sumcheck<NUM_VARS, COMPOSITION_SIZE, DATA_IS_TRANSPOSED> (sumcheck/sumcheck.cuh:10-300): prover for the sum over the
+    hypercube of a product of `composition_size` multilinears over GF(2^128).  `evals`: composition_size columns of
+    2^num_vars evaluations as 32-bit words, compact or (data_is_transposed) bit-sliced in batches of 32 -- a host numpy
+    array (copied, as the reference's constructor does) or a CUDA tensor (adopted and overwritten in place)."""
+
+    def __init__(self, evals, num_vars, composition_size, data_is_transposed=False, device=None):
+        import torch
+
+        if device is None:
+            device = evals.device.index if isinstance(evals, torch.Tensor) and evals.is_cuda else torch.cuda.current_device()
+        self.num_vars, self.composition_size = num_vars, composition_size
+        self._h = C.c_void_p()
+        _check(lib().b2ntt_sumcheck_create(C.byref(self._h), num_vars, composition_size, device), "b2ntt_sumcheck_create")
+        words = 4 * composition_size << num_vars
+        if isinstance(evals, torch.Tensor) and evals.is_cuda:
+            if evals.numel() != words or evals.element_size() != 4 or not evals.is_contiguous():
+                raise ValueError("Sumcheck: evals must be a contiguous tensor of composition_size * 2^num_vars * 4 32-bit words")
+            self._keep = evals
+            _check(lib().b2ntt_sumcheck_load_device(self._h, evals.data_ptr(), int(data_is_transposed)), "b2ntt_sumcheck_load_device")
+        else:
+            import numpy as np
+
+            h = np.ascontiguousarray(evals, dtype=np.uint32).reshape(-1)
+            if h.size != words:
+                raise ValueError("Sumcheck: evals must hold composition_size * 2^num_vars * 4 32-bit words")
+            _check(lib().b2ntt_sumcheck_load_host(self._h, h.ctypes.data, int(data_is_transposed)), "b2ntt_sumcheck_load_host")
+
+    def this_round_messages(self):
+        """-> (sum[4], points[composition_size + 1][4]) as uint32 arrays"""
+        import numpy as np
+
+        s = np.zeros(4, dtype=np.uint32)
+        p = np.zeros(4 * (self.composition_size + 1), dtype=np.uint32)
+        _check(lib().b2ntt_sumcheck_round_messages(self._h, s.ctypes.data, p.ctypes.data), "b2ntt_sumcheck_round_messages")
+        return s, p.reshape(-1, 4)
+
+    def move_to_next_round(self, challenge):
+        import numpy as np
+
+        c = np.ascontiguousarray(challenge, dtype=np.uint32).reshape(-1)
+        if c.size != 4:
+            raise ValueError("Sumcheck: a challenge is 4 32-bit words")
+        _check(lib().b2ntt_sumcheck_next_round(self._h, c.ctypes.data), "b2ntt_sumcheck_next_round")
+
+    @property
+    def round(self):
+        return lib().b2ntt_sumcheck_round(self._h)
+
+    @property
+    def launches(self):
+        return lib().b2ntt_sumcheck_launches(self._h)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().b2ntt_sumcheck_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -34,4 +34,7 @@ int launch_bitslice(uint32_t* d, uint64_t n_blocks, int width_bits, int dir, cud
 int launch_mul(int field_bits, int layout, const uint32_t* a, const uint32_t* b, uint32_t* out, uint64_t n, cudaStream_t stream);
 int launch_mul_repeat(int field_bits, uint32_t* io, uint64_t n_threads, int iters, cudaStream_t stream);
 
+// records the CUDA error text for b2ntt_last_cuda_error() and returns B2NTT_ECUDA (b2ntt.cu)
+int report_cuda_error(cudaError_t e, const char* where);
+
 }  // namespace b2

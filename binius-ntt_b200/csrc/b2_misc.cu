@@ -7,6 +7,7 @@
 
 #include "b2_bundle.cuh"
 #include "b2_launch.h"
+#include "b2_mul128.cuh"
 
 namespace b2 {
 
@@ -165,64 +166,8 @@ __global__ void __launch_bounds__(128) mul_sliced32_kernel(const uint32_t* __res
 	}
 }
 
-// bit-sliced GF(2^128): a block is 4 limbs x 32 words.  Two Karatsuba levels above GF(2^32) give
-// nine GF(2^32) products; FOUR threads share one block so that each holds at most one 32-word
-// operand pair plus accumulators.  Thread q of the quad computes the products of one GF(2^64)
-// sub-problem and the quad combines through shared memory.
-//   A = (A0, A1), A0 = (a0, a1), A1 = (a2, a3) over GF(2^64); the three GF(2^64) products
-//   Z0 = A0*B0, Z2 = A1*B1, ZZ = (A0+A1)*(B0+B1) go to threads 0..2 (thread 3 helps with stores).
-__device__ __forceinline__ void load32(const uint32_t* p, uint32_t* w) {
-	const uint4* q = reinterpret_cast<const uint4*>(p);
-#pragma unroll
-	for (int i = 0; i < 8; i++) {
-		const uint4 u = q[i];
-		w[4 * i] = u.x, w[4 * i + 1] = u.y, w[4 * i + 2] = u.z, w[4 * i + 3] = u.w;
-	}
-}
-
-// GF(2^64) product of (x0,x1)*(y0,y1) given as 32-word halves read through `ld` from two sources
-// (the operand is src0[limb] ^ src1[limb] when two = true).  out: 64 words.
-__device__ __forceinline__ void sliced64_mul_from(const uint32_t* a0p, const uint32_t* a1p, const uint32_t* b0p, const uint32_t* b1p,
-                                                  bool two, int limb0, uint32_t* out /*64*/) {
-	uint32_t x[32], y[32], t[32], z0[32], z2[32];
-	auto ld = [&](const uint32_t* p0, const uint32_t* p1, int limb, uint32_t* w) {
-		load32(p0 + 32 * limb, w);
-		if (two) {
-			uint32_t u[32];
-			load32(p1 + 32 * limb, u);
-#pragma unroll
-			for (int i = 0; i < 32; i++) w[i] ^= u[i];
-		}
-	};
-	ld(a0p, a1p, limb0, x), ld(b0p, b1p, limb0, y);
-	Sliced<5>::mul(x, y, z0);
-	ld(a0p, a1p, limb0 + 1, t);
-#pragma unroll
-	for (int i = 0; i < 32; i++) x[i] ^= t[i];
-	ld(b0p, b1p, limb0 + 1, t);
-#pragma unroll
-	for (int i = 0; i < 32; i++) y[i] ^= t[i];
-	Sliced<5>::mul(x, y, out + 32);  // zz
-	ld(a0p, a1p, limb0 + 1, x), ld(b0p, b1p, limb0 + 1, y);
-	Sliced<5>::mul(x, y, z2);
-	Sliced<5>::mul_alpha(z2, t);
-#pragma unroll
-	for (int i = 0; i < 32; i++) {
-		const uint32_t lo = z0[i] ^ z2[i];
-		out[i] = lo;
-		out[32 + i] ^= lo ^ t[i];
-	}
-}
-
-// bit-sliced GF(2^128), 32 blocks (16 KB per operand) per CTA iteration.  Two Karatsuba levels above GF(2^32) give
-// nine GF(2^32) products per block: warp j of the 9 warps computes product j for the 32 blocks (lane = block), so a
-// thread holds one 32-word operand pair and its product.  Operands arrive by coalesced cp.async into padded rows
-// (pitch 132 words: conflict-free 16-byte reads of 8 different rows), the products are combined through shared
-// memory in two linear steps and the result rows leave by coalesced 16-byte stores.
-//   j = 3u + v:  u = 0: A0 = (a0, a1), 1: A1 = (a2, a3), 2: A0 + A1;  v = 0: low limb, 1: high limb, 2: their sum
-//   Z_u = (P_3u + P_3u+1,  P_3u+2 + P_3u + P_3u+1 + alpha5 * P_3u+1)           (GF(2^64) products)
-//   out = (Z_0 + Z_1,  Z_2 + Z_0 + Z_1 + alpha6 * Z_1),  alpha6 * (lo, hi) = (hi, lo + alpha5 * hi)
-constexpr int kMulPitch = 132, kProdPitch = 33;
+// bit-sliced GF(2^128), 32 blocks (16 KB per operand) per CTA iteration: operands arrive by coalesced cp.async into the
+// padded rows of b2_mul128.cuh, cta_mul128 multiplies, the result rows leave by coalesced 16-byte stores.
 #ifndef B2_MUL128_CTAS
 #define B2_MUL128_CTAS 2  // 96 registers per thread (a few spilled words), two CTAs = 18 warps per SM: 9.1 ms vs 11.7 ms at one CTA
 #endif
@@ -231,16 +176,14 @@ constexpr int kMulPitch = 132, kProdPitch = 33;
 // the product runs bit-sliced as above and warps 0..3 transpose the result rows back before the store.  n_chunks = number
 // of valid 16-byte chunks (= elements when compact), so a ragged last block is neither read nor written past its end.
 template <bool COMPACT>
-__global__ void __launch_bounds__(288, B2_MUL128_CTAS) mul_sliced128_kernel(const uint32_t* __restrict__ a, const uint32_t* __restrict__ b, uint32_t* __restrict__ o, uint64_t n_blocks, uint64_t n_chunks) {
+__global__ void __launch_bounds__(kMulThreads, B2_MUL128_CTAS) mul_sliced128_kernel(const uint32_t* __restrict__ a, const uint32_t* __restrict__ b, uint32_t* __restrict__ o, uint64_t n_blocks, uint64_t n_chunks) {
 	extern __shared__ __align__(16) uint32_t msm[];
-	uint32_t* sa = msm;                        // [32][132] operand a, later the result rows
-	uint32_t* sb = msm + 32 * kMulPitch;       // [32][132] operand b
-	uint32_t* sp = sb + 32 * kMulPitch;        // [9][32][33] products P_j
-	uint32_t* sz = sp + 9 * 32 * kProdPitch;   // [6][32][33] Z_u low / high halves
-	const int j = threadIdx.x >> 5, lb = threadIdx.x & 31, u = j / 3, v = j - 3 * u;
+	const MulSmem m = mul_smem_view(msm);
+	uint32_t *sa = m.sa, *sb = m.sb;
+	const int j = threadIdx.x >> 5, lb = threadIdx.x & 31;
 	for (uint64_t g0 = (uint64_t)blockIdx.x * 32; g0 < n_blocks; g0 += (uint64_t)gridDim.x * 32) {
 		const int nact = n_blocks - g0 < 32 ? (int)(n_blocks - g0) : 32;
-		for (int ch = threadIdx.x; ch < nact * 32; ch += 288) {  // 16-byte chunks: 32 per block row
+		for (int ch = threadIdx.x; ch < nact * 32; ch += kMulThreads) {  // 16-byte chunks: 32 per block row
 			const int row = ch >> 5, c4 = (ch & 31) * 4;
 			if ((g0 + row) * 32 + (ch & 31) >= n_chunks) continue;
 			const unsigned da = (unsigned)__cvta_generic_to_shared(sa + row * kMulPitch + c4), db = (unsigned)__cvta_generic_to_shared(sb + row * kMulPitch + c4);
@@ -263,74 +206,7 @@ __global__ void __launch_bounds__(288, B2_MUL128_CTAS) mul_sliced128_kernel(cons
 			}
 			__syncthreads();
 		}
-		const bool act = lb < nact;
-		if (act) {
-			// operand limbs of product j: limbs {l0} (+ {l0 + 1} when v = 2), the same from the other half when u = 2
-			uint32_t x[32], y[32], t[32];
-			const uint32_t *pa = sa + lb * kMulPitch, *pb = sb + lb * kMulPitch;
-			const int base = u == 1 ? 2 : 0, l0 = base + (v == 1 ? 1 : 0);
-			load32(pa + 32 * l0, x), load32(pb + 32 * l0, y);
-			if (v == 2) {
-				load32(pa + 32 * (l0 + 1), t);
-#pragma unroll
-				for (int i = 0; i < 32; i++) x[i] ^= t[i];
-				load32(pb + 32 * (l0 + 1), t);
-#pragma unroll
-				for (int i = 0; i < 32; i++) y[i] ^= t[i];
-			}
-			if (u == 2) {
-				load32(pa + 32 * (l0 + 2), t);
-#pragma unroll
-				for (int i = 0; i < 32; i++) x[i] ^= t[i];
-				load32(pb + 32 * (l0 + 2), t);
-#pragma unroll
-				for (int i = 0; i < 32; i++) y[i] ^= t[i];
-				if (v == 2) {
-					load32(pa + 32 * (l0 + 3), t);
-#pragma unroll
-					for (int i = 0; i < 32; i++) x[i] ^= t[i];
-					load32(pb + 32 * (l0 + 3), t);
-#pragma unroll
-					for (int i = 0; i < 32; i++) y[i] ^= t[i];
-				}
-			}
-			Sliced<5>::mul(x, y, t);
-#pragma unroll
-			for (int i = 0; i < 32; i++) sp[(j * 32 + lb) * kProdPitch + i] = t[i];
-		}
-		__syncthreads();
-		if (act && j < 6) {  // Z_u halves: warp 2u -> low, warp 2u + 1 -> high
-			const int uu = j >> 1;
-			const uint32_t *p0 = sp + ((3 * uu) * 32 + lb) * kProdPitch, *p1 = p0 + 32 * kProdPitch, *p2 = p1 + 32 * kProdPitch;
-			uint32_t* z = sz + (j * 32 + lb) * kProdPitch;
-			if (!(j & 1)) {
-				for (int i = 0; i < 32; i++) z[i] = p0[i] ^ p1[i];
-			} else {
-				uint32_t q[32], aq[32];
-				for (int i = 0; i < 32; i++) q[i] = p1[i];
-				Sliced<5>::mul_alpha(q, aq);
-				for (int i = 0; i < 32; i++) z[i] = p2[i] ^ p0[i] ^ q[i] ^ aq[i];
-			}
-		}
-		__syncthreads();
-		if (act && j < 4) {  // result limb j of the block, into the row that held operand a
-			const uint32_t *z0l = sz + lb * kProdPitch, *z0h = z0l + 32 * kProdPitch, *z1l = z0h + 32 * kProdPitch, *z1h = z1l + 32 * kProdPitch,
-			               *z2l = z1h + 32 * kProdPitch, *z2h = z2l + 32 * kProdPitch;
-			uint32_t* po = sa + lb * kMulPitch + 32 * j;
-			if (j == 0) {
-				for (int i = 0; i < 32; i++) po[i] = z0l[i] ^ z1l[i];
-			} else if (j == 1) {
-				for (int i = 0; i < 32; i++) po[i] = z0h[i] ^ z1h[i];
-			} else if (j == 2) {
-				for (int i = 0; i < 32; i++) po[i] = z2l[i] ^ z0l[i] ^ z1l[i] ^ z1h[i];
-			} else {
-				uint32_t q[32], aq[32];
-				for (int i = 0; i < 32; i++) q[i] = z1h[i];
-				Sliced<5>::mul_alpha(q, aq);
-				for (int i = 0; i < 32; i++) po[i] = z2h[i] ^ z0h[i] ^ q[i] ^ z1l[i] ^ aq[i];
-			}
-		}
-		__syncthreads();
+		cta_mul128(sa, sb, m.sp, m.sz, nact);
 		if (COMPACT) {
 			if (j < 4) {
 				uint32_t r[32];
@@ -345,7 +221,7 @@ __global__ void __launch_bounds__(288, B2_MUL128_CTAS) mul_sliced128_kernel(cons
 			}
 			__syncthreads();
 		}
-		for (int ch = threadIdx.x; ch < nact * 32; ch += 288) {
+		for (int ch = threadIdx.x; ch < nact * 32; ch += kMulThreads) {
 			const int row = ch >> 5, c4 = (ch & 31) * 4;
 			if ((g0 + row) * 32 + (ch & 31) >= n_chunks) continue;
 			*reinterpret_cast<uint4*>(o + (g0 + row) * 128 + c4) = *reinterpret_cast<const uint4*>(sa + row * kMulPitch + c4);
@@ -353,7 +229,6 @@ __global__ void __launch_bounds__(288, B2_MUL128_CTAS) mul_sliced128_kernel(cons
 		__syncthreads();
 	}
 }
-constexpr size_t kMulSmemBytes = (2 * 32 * kMulPitch + 15 * 32 * kProdPitch) * sizeof(uint32_t);
 
 int launch_mul(int field_bits, int layout, const uint32_t* a, const uint32_t* b, uint32_t* o, uint64_t n, cudaStream_t stream) {
 	if (n == 0) return 0;
@@ -374,7 +249,7 @@ int launch_mul(int field_bits, int layout, const uint32_t* a, const uint32_t* b,
 				blocks = (unsigned)((nb + 31) / 32);
 				if (blocks > cap) blocks = cap;
 				cudaFuncSetAttribute(mul_sliced128_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMulSmemBytes);
-				mul_sliced128_kernel<true><<<blocks, 288, kMulSmemBytes, stream>>>(a, b, o, nb, n);
+				mul_sliced128_kernel<true><<<blocks, kMulThreads, kMulSmemBytes, stream>>>(a, b, o, nb, n);
 				break;
 			}
 			default: return -1;
@@ -390,7 +265,7 @@ int launch_mul(int field_bits, int layout, const uint32_t* a, const uint32_t* b,
 			unsigned blocks = (unsigned)((nb + 31) / 32);
 			if (blocks > cap) blocks = cap;
 			cudaFuncSetAttribute(mul_sliced128_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMulSmemBytes);
-			mul_sliced128_kernel<false><<<blocks, 288, kMulSmemBytes, stream>>>(a, b, o, nb, nb * 32);
+			mul_sliced128_kernel<false><<<blocks, kMulThreads, kMulSmemBytes, stream>>>(a, b, o, nb, nb * 32);
 		} else
 			return -1;
 	}

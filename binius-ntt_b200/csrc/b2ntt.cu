@@ -21,6 +21,9 @@ static int cuda_fail(cudaError_t e, const char* where) {
 	cudaGetLastError();
 	return B2NTT_ECUDA;
 }
+namespace b2 {
+int report_cuda_error(cudaError_t e, const char* where) { return cuda_fail(e, where); }
+}  // namespace b2
 #define CU(call)                                              \
 	do {                                                      \
 		cudaError_t e_ = (call);                              \

@@ -126,6 +126,27 @@ int b2ntt_mul_repeat(int field_bits, void* d_io, size_t n_threads, int iters, vo
 /* Replaces bool check_gpu_capabilities() (utils/common.cu:6-43): 1 capable, 0 not, <0 error. */
 int b2ntt_check_gpu_capabilities(int device);
 
+/* ---- bit-sliced GF(2^128) sumcheck prover for a product of `composition_size` multilinears ----
+ * Replaces Sumcheck<NUM_VARS, COMPOSITION_SIZE, DATA_IS_TRANSPOSED> (sumcheck/sumcheck.cuh:10-300) and its kernels
+ * compute_compositions (sumcheck/core/kernels.cuh:5-102) / fold_large_list_halves (sumcheck/core/kernels.cu:9-30).
+ * num_vars 5..30 (the reference instantiates 20, 24, 28), composition_size 2..4. */
+typedef struct b2ntt_sumcheck b2ntt_sumcheck;
+int b2ntt_sumcheck_create(b2ntt_sumcheck** sc, int num_vars, int composition_size, int device);
+int b2ntt_sumcheck_destroy(b2ntt_sumcheck* sc);
+/* The constructor's upload (sumcheck.cuh:79-126): composition_size columns of 2^num_vars GF(2^128) evaluations, compact
+ * (transposed = 0: bit-sliced on the device first, transpose_kernel<128>) or already bit-sliced (transposed = 1).
+ * load_host copies into a buffer the object owns; load_device adopts the caller's device buffer, which the protocol
+ * then overwrites in place.  Either call restarts the protocol at round 0. */
+int b2ntt_sumcheck_load_host(b2ntt_sumcheck* sc, const void* h_evals, int transposed);
+int b2ntt_sumcheck_load_device(b2ntt_sumcheck* sc, void* d_evals, int transposed);
+/* this_round_messages (sumcheck.cuh:136-246): sum[4] = XOR over the remaining hypercube of the product; points[(C+1)*4] =
+ * the round polynomial at t = 0..C.  Valid for rounds 0..num_vars (the last call returns the final evaluation claim). */
+int b2ntt_sumcheck_round_messages(b2ntt_sumcheck* sc, uint32_t* sum, uint32_t* points);
+/* move_to_next_round (sumcheck.cuh:248-299): binds the top remaining variable to challenge[4]. */
+int b2ntt_sumcheck_next_round(b2ntt_sumcheck* sc, const uint32_t* challenge);
+int b2ntt_sumcheck_round(const b2ntt_sumcheck* sc);
+long long b2ntt_sumcheck_launches(const b2ntt_sumcheck* sc);
+
 const char* b2ntt_strerror(int code);
 /* Text of the last CUDA error seen by the calling thread's last failing call ("" if none). */
 const char* b2ntt_last_cuda_error(void);

@@ -88,6 +88,16 @@ const char* orc_golden_md5(int log_rate, int log_h);
 
 int orc_num_threads(void);
 
+/* ---- bit-sliced GF(2^128) sumcheck prover + verifier, compact restatement (sumcheck.c; sumcheck/sumcheck.cuh:10-300,
+ *      sumcheck/core/core.cu:9-96, sumcheck/test/verifier.cu:9-107) ---- */
+struct orc_sc;
+struct orc_sc* orc_sc_create(const uint32_t* evals /* comp columns of 2^num_vars compact elements */, int num_vars, int comp);
+void orc_sc_destroy(struct orc_sc* s);
+void orc_sc_round_messages(const struct orc_sc* s, uint32_t sum[4], uint32_t* points /* (comp + 1) * 4 */);
+void orc_sc_next_round(struct orc_sc* s, const uint32_t challenge[4]);
+void orc_sc_interpolate(const uint32_t challenge[4], const uint32_t* points, int num_points, uint32_t out[4]);
+void orc_sc_eval_composition(const uint32_t* evals, const uint32_t* challenges, int num_vars, int comp, uint32_t out[4]);
+
 #ifdef __cplusplus
 }
 #endif

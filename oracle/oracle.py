@@ -56,6 +56,13 @@ def _load():
     lib.orc_golden_md5.argtypes = [C.c_int, C.c_int]
     lib.orc_golden_md5.restype = C.c_char_p
     lib.orc_num_threads.restype = C.c_int
+    lib.orc_sc_create.argtypes = [_u32p, C.c_int, C.c_int]
+    lib.orc_sc_create.restype = C.c_void_p
+    lib.orc_sc_destroy.argtypes = [C.c_void_p]
+    lib.orc_sc_round_messages.argtypes = [C.c_void_p, _u32p, _u32p]
+    lib.orc_sc_next_round.argtypes = [C.c_void_p, _u32p]
+    lib.orc_sc_interpolate.argtypes = [_u32p, _u32p, C.c_int, _u32p]
+    lib.orc_sc_eval_composition.argtypes = [_u32p, _u32p, C.c_int, C.c_int, _u32p]
     for name in ("orc_tower_mul", "orc_tower_square", "orc_tower_inverse", "orc_tower_mul_alpha"):
         pass  # 128-bit by-value arguments are not expressible in ctypes; use the word forms
     return lib
@@ -183,3 +190,43 @@ def mul_bitsliced(a, b, h):
     for i in range(a.shape[0]):
         lib.orc_mul_bitsliced(a[i], b[i], out[i], h)
     return out.reshape(-1)
+
+
+class Sumcheck:
+    """Compact restatement of Sumcheck<NUM_VARS, COMPOSITION_SIZE, *> (sumcheck/sumcheck.cuh:10-300); evals: COMPACT
+    GF(2^128) words, composition_size columns of 2^num_vars elements."""
+
+    def __init__(self, evals, num_vars, composition_size):
+        evals = np.ascontiguousarray(evals, dtype=np.uint32).reshape(-1)
+        assert evals.size == 4 * composition_size << num_vars
+        self.num_vars, self.comp = num_vars, composition_size
+        self._h = lib.orc_sc_create(evals, num_vars, composition_size)
+
+    def this_round_messages(self):
+        s = np.zeros(4, dtype=np.uint32)
+        p = np.zeros(4 * (self.comp + 1), dtype=np.uint32)
+        lib.orc_sc_round_messages(self._h, s, p)
+        return s, p.reshape(-1, 4)
+
+    def move_to_next_round(self, challenge):
+        lib.orc_sc_next_round(self._h, np.ascontiguousarray(challenge, dtype=np.uint32))
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib.orc_sc_destroy(self._h)
+            self._h = None
+
+
+def sc_interpolate(challenge, points):
+    """evaluate_univariate_given_points (sumcheck/test/verifier.cu:9-31)"""
+    points = np.ascontiguousarray(points, dtype=np.uint32).reshape(-1, 4)
+    out = np.zeros(4, dtype=np.uint32)
+    lib.orc_sc_interpolate(np.ascontiguousarray(challenge, dtype=np.uint32), points.reshape(-1), points.shape[0], out)
+    return out
+
+
+def sc_eval_composition(evals, challenges, num_vars, composition_size):
+    """evaluate_multilinear_composition (sumcheck/test/verifier.cu:92-107), brute force"""
+    out = np.zeros(4, dtype=np.uint32)
+    lib.orc_sc_eval_composition(np.ascontiguousarray(evals, dtype=np.uint32).reshape(-1), np.ascontiguousarray(challenges, dtype=np.uint32).reshape(-1), num_vars, composition_size, out)
+    return out

@@ -169,3 +169,30 @@ def test_plan_constants_and_products_match_oracle(oracle, emul):
         out = np.empty(1 << h, dtype=np.uint32)
         emul.emul_sliced_mul(a, b, out, h)
         assert np.array_equal(out, oracle.mul_bitsliced(a, b, h))
+
+
+# ---- sumcheck restatement: the reference's own test protocol (sumcheck/test/test.cu:16-96) ------------------------
+def run_sumcheck_protocol(prover, evals_compact, num_vars, comp, oracle, seed, brute_force=True):
+    """Drives `prover` (this_round_messages / move_to_next_round) the way test_sumcheck does and applies its REQUIREs."""
+    rng = np.random.default_rng(seed)
+    challenges, expected = [], None
+    for rnd in range(num_vars):
+        s, pts = prover.this_round_messages()
+        assert rnd == 0 or np.array_equal(s, expected), ("claim", rnd)
+        assert np.array_equal(s, pts[0] ^ pts[1]), ("sum = p(0) + p(1)", rnd)
+        ch = rng.integers(0, 2**32, 4, dtype=np.uint32)
+        challenges.append(ch)
+        expected = oracle.sc_interpolate(ch, pts)
+        prover.move_to_next_round(ch)
+    s, _ = prover.this_round_messages()
+    assert np.array_equal(s, expected), "final claim"
+    if brute_force:
+        assert np.array_equal(oracle.sc_eval_composition(evals_compact, np.stack(challenges), num_vars, comp), expected)
+    return expected
+
+
+@pytest.mark.parametrize("comp", [2, 3, 4])
+def test_sumcheck_restatement_passes_the_reference_verifier(oracle, comp):
+    for num_vars in (1, 5, 6, 9):
+        evals = _rand(4 * comp << num_vars, 100 * comp + num_vars)
+        run_sumcheck_protocol(oracle.Sumcheck(evals, num_vars, comp), evals, num_vars, comp, oracle, seed=num_vars)
