@@ -10,12 +10,16 @@
 //     f_c = lo_c ^ t * (lo_c ^ hi_c) (t = 0: lo, t = 1: hi; t >= 2: a GF(16) constant product on each 4-word group),
 //     multiplies the C columns with the CTA-level product of b2_mul128.cuh and XORs the 32 product rows into a per-CTA
 //     accumulator; one atomicXor per word per CTA at the end.  The claimed sum is points[0] ^ points[1] (the same XOR
-//     of all 2^(num_vars-i) products the reference forms separately).
+//     of all 2^(num_vars-i) products the reference forms separately).  From the second round on p(1) is not computed
+//     on the device: the folded multilinears sum to q(r), q the previous round polynomial (degree C, known at C + 1
+//     points) and r the challenge just bound, so p(1) = q(r) ^ p(0) exactly -- (C - 1) of the (C + 1)(C - 1) + C
+//     products per pair less.
 //   fold kernel: a_c[x] <- lo ^ r * (lo ^ hi), r broadcast to all 32 positions.
 // With 32 or fewer evaluations left the reference moves to the host (sumcheck.cuh:159-191, fold_small core.cu:57-79); so
 // does this file, on the compact values of the last batch (a few hundred field products).
 #include <cuda_runtime.h>
 
+#include <cstring>
 #include <new>
 #include <vector>
 
@@ -40,7 +44,7 @@ __device__ __forceinline__ uint4 sc_point(const uint4 lo, const uint4 hi, int t)
 }
 
 // out[(C + 1) * 128] ^= per-point XOR over the batch rows [0, half_rows) of PROD_c f_c
-__global__ void __launch_bounds__(kMulThreads, 2) sc_round_kernel(const uint32_t* __restrict__ evals, uint64_t col_words, uint64_t half_rows, int C, uint32_t* out) {
+__global__ void __launch_bounds__(kMulThreads, 2) sc_round_kernel(const uint32_t* __restrict__ evals, uint64_t col_words, uint64_t half_rows, int C, int skip1, uint32_t* out) {
 	extern __shared__ __align__(16) uint32_t msm[];
 	const MulSmem m = mul_smem_view(msm);
 	uint32_t* acc = msm + kMulSmemWords;  // [(C + 1)][128]
@@ -49,6 +53,7 @@ __global__ void __launch_bounds__(kMulThreads, 2) sc_round_kernel(const uint32_t
 		const int nact = half_rows - g0 < 32 ? (int)(half_rows - g0) : 32;
 #pragma unroll 1
 		for (int t = 0; t <= C; t++) {
+			if (t == 1 && skip1) continue;  // the host derives p(1) from the verifier's claim
 #pragma unroll 1
 			for (int c = 1; c < C; c++) {
 				// stage column c into sb and, for the first product, column 0 into sa
@@ -134,6 +139,10 @@ struct b2ntt_sumcheck {
 	bool owns_evals = false;
 	uint32_t *d_out = nullptr, *d_coeff = nullptr;
 	std::vector<gf128> tail;  // [C][32] compact values once 32 or fewer evaluations are left
+	uint32_t last_points[(kScMaxC + 1) * 4] = {0};
+	int points_round = -1;    // round whose points are in last_points
+	gf128 claim{};            // q(r) of the round before the current one
+	bool have_claim = false;
 	bool loaded = false;
 	uint64_t launches = 0;
 };
@@ -143,6 +152,25 @@ struct b2ntt_sumcheck {
 		cudaError_t e_ = (call);                                   \
 		if (e_ != cudaSuccess) return report_cuda_error(e_, #call); \
 	} while (0)
+
+// Lagrange evaluation at r of the polynomial through (t, points[t]), t = 0..np-1 (what the verifier computes,
+// evaluate_univariate_given_points, sumcheck/test/verifier.cu:9-31); the nodes lie in GF(16)
+static gf128 sc_interpolate(const uint32_t* points, int np, const gf128& r) {
+	gf128 e{};
+	for (int i = 0; i < np; i++) {
+		gf128 p;
+		for (int k = 0; k < 4; k++) p.w[k] = points[4 * i + k];
+		for (int j = 0; j < np; j++)
+			if (j != i) {
+				gf128 f = r, inv{};
+				f.w[0] ^= (uint32_t)j;
+				inv.w[0] = (uint32_t)Tower<2>::inverse((uint64_t)(i ^ j));
+				p = gf128_mul(gf128_mul(p, f), inv);
+			}
+		e = gx(e, p);
+	}
+	return e;
+}
 
 static int sc_fetch_tail(b2ntt_sumcheck* s) {
 	std::vector<uint32_t> batch(128);
@@ -191,7 +219,7 @@ static int sc_adopt(b2ntt_sumcheck* s, int transposed) {
 		if (launch_bitslice(s->d_evals, s->n0 / 32 * s->C, 128, 0, nullptr)) return B2NTT_ECUDA;
 		s->launches++;
 	}
-	s->round = 0, s->loaded = true;
+	s->round = 0, s->loaded = true, s->points_round = -1, s->have_claim = false;
 	s->tail.clear();
 	if (s->n0 == 32) {
 		SCU(cudaDeviceSynchronize());
@@ -248,6 +276,7 @@ extern "C" int b2ntt_sumcheck_round_messages(b2ntt_sumcheck* s, uint32_t* sum, u
 			}
 			for (int i = 0; i < 4; i++) points[4 * t + i] = pt.w[i];
 		}
+		memcpy(s->last_points, points, (C + 1) * 16), s->points_round = s->round;
 		return B2NTT_OK;
 	}
 	SCU(cudaSetDevice(s->device));
@@ -256,7 +285,8 @@ extern "C" int b2ntt_sumcheck_round_messages(b2ntt_sumcheck* s, uint32_t* sum, u
 	uint64_t ctas = (half_rows + 31) / 32;
 	if (ctas > (uint64_t)s->sms * 2) ctas = (uint64_t)s->sms * 2;
 	const size_t smem = (kMulSmemWords + (C + 1) * 128) * sizeof(uint32_t);
-	sc_round_kernel<<<(unsigned)ctas, kMulThreads, smem>>>(s->d_evals, s->n0 * 4, half_rows, C, s->d_out);
+	const int skip1 = s->have_claim ? 1 : 0;
+	sc_round_kernel<<<(unsigned)ctas, kMulThreads, smem>>>(s->d_evals, s->n0 * 4, half_rows, C, skip1, s->d_out);
 	SCU(cudaGetLastError());
 	s->launches++;
 	std::vector<uint32_t> h((C + 1) * 128);
@@ -268,13 +298,22 @@ extern "C" int b2ntt_sumcheck_round_messages(b2ntt_sumcheck* s, uint32_t* sum, u
 		for (int x = 0; x < 32; x++) acc = gx(acc, e[x]);
 		for (int i = 0; i < 4; i++) points[4 * t + i] = acc.w[i];
 	}
+	if (skip1)
+		for (int i = 0; i < 4; i++) points[4 + i] = s->claim.w[i] ^ points[i];
 	for (int i = 0; i < 4; i++) sum[i] = points[i] ^ points[4 + i];
+	memcpy(s->last_points, points, (C + 1) * 16), s->points_round = s->round;
 	return B2NTT_OK;
 }
 
 extern "C" int b2ntt_sumcheck_next_round(b2ntt_sumcheck* s, const uint32_t* challenge) {
 	if (!s || !challenge || !s->loaded || s->round >= s->num_vars) return B2NTT_EINVAL;
 	const uint64_t n = s->n0 >> s->round;
+	{
+		gf128 r;
+		for (int i = 0; i < 4; i++) r.w[i] = challenge[i];
+		s->have_claim = s->points_round == s->round;
+		if (s->have_claim) s->claim = sc_interpolate(s->last_points, s->C + 1, r);
+	}
 	if (n <= 32) {
 		const int half = (int)(n / 2);
 		gf128 r;

@@ -88,6 +88,12 @@ def ref_lib():
     r.ref_bitslice.argtypes = [_u32p, C.c_int]
     r.ref_unbitslice.argtypes = [_u32p, C.c_int]
     r.ref_mul128_words.argtypes = [_u32p, _u32p, _u32p]
+    if hasattr(r, "ref_sc_compose"):
+        r.ref_sc_compose.argtypes = [_u32p, _u32p, C.c_uint32, C.c_uint32]
+        r.ref_sc_fold_batch.argtypes = [_u32p, _u32p, _u32p, _u32p, C.c_int]
+        r.ref_sc_fold_small.argtypes = [_u32p, _u32p, _u32p, C.c_uint32]
+        r.ref_sc_compute_sum.argtypes = [_u32p, _u32p, C.c_uint32]
+        r.ref_sc_repeat_value.argtypes = [_u32p, _u32p]
     return r
 
 

@@ -16,6 +16,7 @@
 #include "ulvt/finite_fields/circuit_generator/utils/utils.hpp"
 #include "ulvt/finite_fields/circuit_generator/unrolled/binary_tower_unrolled.cuh"
 #include "ulvt/ntt/additive_ntt.cuh"
+#include "ulvt/sumcheck/sumcheck.cuh"
 #include "ulvt/utils/bitslicing.cuh"
 
 static int g_failed = 0, g_checks = 0;
@@ -63,6 +64,41 @@ static bool run_and_check_additive_ntt128(int log_h, int log_rate) {
 	orc_md5_hex(limb0.data(), limb0.size() * 4, hex);
 	const char* want = orc_golden_md5(log_rate, log_h);
 	return want && strcmp(hex, want) == 0;
+}
+
+// sumcheck/test/test.cu:16-96 (test_sumcheck<NUM_VARS, COMPOSITION_SIZE, DATA_IS_TRANSPOSED>) with the verifier of
+// sumcheck/test/verifier.cu restated by the oracle; seeded instead of time-seeded
+template <uint32_t NUM_VARS, uint32_t COMPOSITION_SIZE, bool DATA_IS_TRANSPOSED>
+static void test_sumcheck() {
+	constexpr uint32_t interpolation_points = COMPOSITION_SIZE + 1;
+	const size_t num_ints_in_evals = INTS_PER_VALUE * ((size_t)1 << NUM_VARS) * COMPOSITION_SIZE;
+	std::mt19937 gen(NUM_VARS * 10 + COMPOSITION_SIZE);
+	std::vector<uint32_t> multilinear_evals(num_ints_in_evals), compact(num_ints_in_evals);
+	for (auto& w : compact) w = gen();
+	multilinear_evals = compact;
+	if (DATA_IS_TRANSPOSED)
+		for (size_t b = 0; b < num_ints_in_evals; b += 128) orc_bitslice(multilinear_evals.data() + b, 128);
+	Sumcheck<NUM_VARS, COMPOSITION_SIZE, DATA_IS_TRANSPOSED> s(multilinear_evals, false);
+	std::vector<uint32_t> challenges(4 * NUM_VARS);
+	std::array<uint32_t, INTS_PER_VALUE> expected_claim{};
+	for (uint32_t round = 0; round < NUM_VARS; ++round) {
+		std::array<uint32_t, INTS_PER_VALUE> sum;
+		std::array<uint32_t, interpolation_points * INTS_PER_VALUE> points;
+		s.this_round_messages(sum, points);
+		CHECK(round == 0 || sum == expected_claim);
+		for (int i = 0; i < 4; i++) CHECK(sum[i] == (points[i] ^ points[4 + i]));
+		std::array<uint32_t, INTS_PER_VALUE> challenge;
+		for (auto& w : challenge) w = gen();
+		memcpy(&challenges[4 * round], challenge.data(), 16);
+		orc_sc_interpolate(challenge.data(), points.data(), interpolation_points, expected_claim.data());
+		s.move_to_next_round(challenge);
+	}
+	std::array<uint32_t, INTS_PER_VALUE> sum, brute;
+	std::array<uint32_t, interpolation_points * INTS_PER_VALUE> points;
+	s.this_round_messages(sum, points);
+	CHECK(sum == expected_claim);
+	orc_sc_eval_composition(compact.data(), challenges.data(), NUM_VARS, COMPOSITION_SIZE, brute.data());
+	CHECK(brute == expected_claim);
 }
 
 template <int H>
@@ -150,6 +186,12 @@ int main(int argc, char** argv) {
 		CHECK(int_to_hex(0xbeefu) == "beef");
 		CHECK(sizeof(KERNEL_LAUNCH_CONFIGS) == 31 * 3 * 2 * sizeof(dim3));
 	}
+
+	// ---- sumcheck (sumcheck/test/test.cu:98-142 at sizes the brute-force check finishes quickly) ----
+	test_sumcheck<12, 2, true>();
+	test_sumcheck<12, 3, false>();
+	test_sumcheck<13, 4, true>();
+	test_sumcheck<14, 2, false>();
 
 	// ---- bit-slicing and the bit-sliced products (tests.cu:125-201, test_fanpaartower.cu:127-273 style) ----
 	{

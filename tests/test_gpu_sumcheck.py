@@ -70,3 +70,32 @@ def test_sumcheck_argument_errors(b2, cuda):
         sc.move_to_next_round(np.ones(4, dtype=np.uint32))
     with pytest.raises(b2.B2NTTError):
         sc.move_to_next_round(np.ones(4, dtype=np.uint32))
+
+
+@pytest.mark.parametrize("comp", [2, 3, 4])
+def test_messages_match_the_reference_cuda_prover(b2, oracle, cuda, comp):
+    """oracle/_ref/ref_sumcheck = the reference's own Sumcheck<20, comp, false> (sumcheck/sumcheck.cuh) built for sm_100a
+    from /root/reference by oracle/Makefile, run on this GPU with seeded inputs: every round's sum and points must be
+    equal word for word."""
+    import os
+    import subprocess
+
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "ref_sumcheck")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/ref_sumcheck not built (needs /root/reference at build time)")
+    nv = 20
+    out = subprocess.run([exe, str(nv), str(comp)], check=True, capture_output=True, text=True, timeout=600).stdout.splitlines()
+    rounds = [ln.split() for ln in out if ln.startswith("round ")]
+    assert len(rounds) == nv + 1
+    evals = oracle.mt19937(0xDEADBEEF + nv + comp, 4 * comp << nv)
+    chal = oracle.mt19937(0xC0FFEE + nv + comp, 4 * nv).reshape(nv, 4)
+    sc = b2.Sumcheck(evals, nv, comp)
+    for rnd, f in enumerate(rounds):
+        assert int(f[1]) == rnd and f[2] == "sum" and f[7] == "points"
+        ref_sum = np.array([int(x, 16) for x in f[3:7]], dtype=np.uint32)
+        ref_pts = np.array([int(x, 16) for x in f[8:]], dtype=np.uint32).reshape(comp + 1, 4)
+        s, p = sc.this_round_messages()
+        assert np.array_equal(s, ref_sum) and np.array_equal(p, ref_pts), (comp, rnd)
+        if rnd < nv:
+            sc.move_to_next_round(chal[rnd])
+    sc.close()

@@ -196,3 +196,98 @@ def test_sumcheck_restatement_passes_the_reference_verifier(oracle, comp):
     for num_vars in (1, 5, 6, 9):
         evals = _rand(4 * comp << num_vars, 100 * comp + num_vars)
         run_sumcheck_protocol(oracle.Sumcheck(evals, num_vars, comp), evals, num_vars, comp, oracle, seed=num_vars)
+
+
+class RefHostSumcheck:
+    """Replays the data flow of the reference's Sumcheck class (sumcheck/sumcheck.cuh:136-299) on the CPU, calling the
+    REFERENCE's own batch helpers (sumcheck/core/core.cu, via oracle/_ref) where the class launches its kernels
+    (compute_compositions, kernels.cuh:5-102; fold_large_list_halves, kernels.cu:9-30)."""
+
+    def __init__(self, R, oracle, evals_compact, num_vars, comp):
+        self.R, self.nv, self.C, self.n0, self.round = R, num_vars, comp, 1 << num_vars, 0
+        self.ev = oracle.bitslice(evals_compact, 128).copy()
+        self.cpu = np.zeros(128 * comp, dtype=np.uint32)
+        self.coeff = np.zeros(128 * (comp + 1), dtype=np.uint32)
+        for t in range(comp + 1):
+            R.ref_sc_repeat_value(self.coeff[128 * t:128 * (t + 1)], np.array([t, 0, 0, 0], dtype=np.uint32))
+        if self.n0 == 32:
+            self.cpu[:] = self.ev
+
+    def this_round_messages(self):
+        R, C, IP = self.R, self.C, self.C + 1
+        n = self.n0 >> self.round
+        padded = max(32, n)
+        s, pts = np.zeros(4, dtype=np.uint32), np.zeros((IP, 4), dtype=np.uint32)
+        fsum = np.zeros(IP * 128, dtype=np.uint32)
+        prod = np.zeros(128, dtype=np.uint32)
+        if padded == 32:
+            R.ref_sc_compose(self.cpu, prod, C, 32)
+            for t in range(IP):
+                folded = np.zeros(128 * C, dtype=np.uint32)
+                for c in range(C):
+                    R.ref_sc_fold_small(self.cpu[128 * c:128 * (c + 1)], folded[128 * c:128 * (c + 1)], self.coeff[128 * t:128 * (t + 1)], n)
+                R.ref_sc_compose(folded, fsum[128 * t:128 * (t + 1)], C, 32)
+            R.ref_sc_compute_sum(s, prod, n)
+            for t in range(IP):
+                R.ref_sc_compute_sum(pts[t], fsum[128 * t:128 * (t + 1)], n // 2)
+            return s, pts
+        rows = padded // 32
+        total = np.zeros(128, dtype=np.uint32)
+        for row in range(rows):
+            R.ref_sc_compose(self.ev[128 * row:], prod, C, self.n0)
+            total ^= prod
+            if row < rows // 2:
+                folded = np.zeros(IP * C * 128, dtype=np.uint32)
+                for c in range(C):
+                    lo = 128 * ((self.n0 // 32) * c + row)
+                    hi = lo + 128 * (rows // 2)
+                    for t in range(IP):
+                        d = 128 * (c * IP + t)
+                        R.ref_sc_fold_batch(self.ev[lo:lo + 128], self.ev[hi:hi + 128], folded[d:d + 128], self.coeff[128 * t:128 * (t + 1)], 1)
+                for t in range(IP):
+                    R.ref_sc_compose(folded[128 * t:], prod, C, IP * 32)
+                    fsum[128 * t:128 * (t + 1)] ^= prod
+        R.ref_sc_compute_sum(s, total, 32)
+        for t in range(IP):
+            R.ref_sc_compute_sum(pts[t], fsum[128 * t:128 * (t + 1)], 32)
+        return s, pts
+
+    def move_to_next_round(self, challenge):
+        R, C = self.R, self.C
+        n = self.n0 >> self.round
+        coeff = np.zeros(128, dtype=np.uint32)
+        R.ref_sc_repeat_value(coeff, np.ascontiguousarray(challenge, dtype=np.uint32))
+        if n <= 32:
+            for c in range(C):
+                col = self.cpu[128 * c:128 * (c + 1)]
+                R.ref_sc_fold_small(col, col, coeff, n)
+        else:
+            half_rows = n >> 6
+            for row in range(half_rows):
+                for c in range(C):
+                    lo = 128 * row + 4 * self.n0 * c
+                    hi = lo + 128 * half_rows
+                    R.ref_sc_fold_batch(self.ev[lo:lo + 128], self.ev[hi:hi + 128], self.ev[lo:lo + 128], coeff, 0)
+            if n // 2 == 32:
+                for c in range(C):
+                    self.cpu[128 * c:128 * (c + 1)] = self.ev[4 * self.n0 * c:4 * self.n0 * c + 128]
+        self.round += 1
+
+
+@pytest.mark.parametrize("comp", [2, 3, 4])
+def test_sumcheck_restatement_matches_reference_batch_code(oracle, comp):
+    """every round message of the compact restatement == the reference's own bit-sliced batch code, same inputs"""
+    R = oracle.ref_lib()
+    if R is None or not hasattr(R, "ref_sc_compose"):
+        pytest.skip("oracle/_ref not built (needs /root/reference)")
+    for num_vars in (5, 7, 8):
+        evals = _rand(4 * comp << num_vars, 31 * comp + num_vars)
+        ref, mine = RefHostSumcheck(R, oracle, evals, num_vars, comp), oracle.Sumcheck(evals, num_vars, comp)
+        rng = np.random.default_rng(num_vars + comp)
+        for rnd in range(num_vars + 1):
+            rs, rp = ref.this_round_messages()
+            s, p = mine.this_round_messages()
+            assert np.array_equal(s, rs) and np.array_equal(p, rp), (num_vars, comp, rnd)
+            if rnd < num_vars:
+                ch = rng.integers(0, 2**32, 4, dtype=np.uint32)
+                ref.move_to_next_round(ch), mine.move_to_next_round(ch)
