@@ -1,9 +1,11 @@
-// ulvt/sumcheck/utils/constants.hpp -- the reference's sumcheck constants (sumcheck/utils/constants.hpp:1-10) that user
-// code names; the launch-shape macros (BLOCKS, THREADS_PER_BLOCK) are not consulted by this implementation.
+// ulvt/sumcheck/utils/constants.hpp -- the names user code takes from the reference's sumcheck/utils/constants.hpp,
+// as typed constants: the field is GF(2^(2^7)), interpolation nodes live in GF(2^(2^2)), a bit-sliced batch is 128 words
+// and a compact value 4 words.  The reference's launch-shape macros have no meaning here and are not provided.
 #pragma once
 #include <cstddef>
-#define TOWER_HEIGHT 7
-#define INTERPOLATION_TOWER_HEIGHT 2
-#define BITS_WIDTH (size_t(1 << TOWER_HEIGHT))
-#define INTERPOLATION_BITS_WIDTH (size_t(1 << INTERPOLATION_TOWER_HEIGHT))
-#define INTS_PER_VALUE (BITS_WIDTH / 32)
+#include <cstdint>
+
+constexpr int TOWER_HEIGHT = 7, INTERPOLATION_TOWER_HEIGHT = 2;
+constexpr std::size_t BITS_WIDTH = std::size_t(1) << TOWER_HEIGHT;
+constexpr std::size_t INTERPOLATION_BITS_WIDTH = std::size_t(1) << INTERPOLATION_TOWER_HEIGHT;
+constexpr std::size_t INTS_PER_VALUE = BITS_WIDTH / 32;

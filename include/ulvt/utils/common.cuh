@@ -1,40 +1,40 @@
-// ulvt/utils/common.cuh -- drop-in for the reference header of the same name (utils/common.cuh:3-32):
-// the ASSERT / CUDA_CHECK macros, the two tile constants and check_gpu_capabilities(), which here
-// forwards to the C ABI (b2ntt_check_gpu_capabilities, include/b2ntt.h).
+// ulvt/utils/common.cuh -- what user code takes from the reference's utils/common.cuh (:3-32): ASSERT and CUDA_CHECK
+// (with their STRIP_* switches), the two tile constants, and check_gpu_capabilities(), which forwards to the C ABI
+// (b2ntt_check_gpu_capabilities, include/b2ntt.h).  The macros are thin wrappers over two inline reporters.
 #pragma once
+#include <cuda_runtime.h>
+
 #include <cstdio>
 #include <cstdlib>
 #include <iostream>
 
 #include "../../b2ntt.h"
 
+namespace b2shim {
+[[noreturn]] inline void assertion_failed(const char* what, const char* file, int line, const char* func) {
+	std::fprintf(stderr, "Assertion failed at %s:%d inside %s\nCondition: %s\n", file, line, func, what);
+	std::abort();
+}
+// CUDA errors are reported, not propagated (the reference's CUDA_CHECK prints and carries on)
+inline void report_cuda(cudaError_t status, const char* file, int line, const char* func) {
+	if (status != cudaSuccess) std::fprintf(stderr, "Cuda error at %s:%d inside %s\nError: %s\n", file, line, func, cudaGetErrorString(status));
+}
+}  // namespace b2shim
+
 #if defined(STRIP_ASSERTIONS)
-#define ASSERT(cond) (cond)
+#define ASSERT(cond) ((void)(cond))
 #else
-#define ASSERT(cond)                                                                                   \
-	do {                                                                                               \
-		if (!(cond)) {                                                                                 \
-			std::cerr << "Assertion failed at " << __FILE__ << ":" << __LINE__ << " inside " << __FUNCTION__ \
-			          << "\nCondition: " << #cond << std::endl;                                        \
-			abort();                                                                                   \
-		}                                                                                              \
-	} while (0)
+#define ASSERT(cond) ((cond) ? (void)0 : b2shim::assertion_failed(#cond, __FILE__, __LINE__, __func__))
 #endif
 
 #if defined(STRIP_CUDA_CHECK)
-#define CUDA_CHECK(call) (call)
+#define CUDA_CHECK(call) ((void)(call))
 #else
-#define CUDA_CHECK(call)                                                                               \
-	do {                                                                                               \
-		cudaError_t b2_err_ = (call);                                                                  \
-		if (b2_err_ != cudaSuccess)                                                                    \
-			std::cerr << "Cuda error at " << __FILE__ << ":" << __LINE__ << " inside " << __FUNCTION__ \
-			          << "\nError: " << cudaGetErrorString(b2_err_) << std::endl;                      \
-	} while (0)
+#define CUDA_CHECK(call) b2shim::report_cuda((call), __FILE__, __LINE__, __func__)
 #endif
 
-#define MAX_SHARED_MEM (1 << 15)
-#define MAX_STAGES_PER_KERNEL 11
+constexpr int MAX_SHARED_MEM = 32 * 1024;     // bytes of static shared memory the reference kernels assumed
+constexpr int MAX_STAGES_PER_KERNEL = 11;     // not consulted by the pass scheduler
 
 // utils/common.cu:6-43 -- device 0, true when the device can run the library
 inline bool check_gpu_capabilities() { return b2ntt_check_gpu_capabilities(0) > 0; }
