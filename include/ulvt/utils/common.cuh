@@ -1,4 +1,4 @@
-// ulvt/utils/common.cuh -- what user code takes from the reference's utils/common.cuh (:3-32): ASSERT and CUDA_CHECK
+// ulvt/utils/common.cuh -- what user code takes from the reference's header (utils/common.cuh:3-32): ASSERT and CUDA_CHECK
 // (with their STRIP_* switches), the two tile constants, and check_gpu_capabilities(), which forwards to the C ABI
 // (b2ntt_check_gpu_capabilities, include/b2ntt.h).  The macros are thin wrappers over two inline reporters.
 #pragma once

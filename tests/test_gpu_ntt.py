@@ -23,7 +23,7 @@ def _rand(n, seed):
 
 # ---- golden digests: the reference's own test, log_rate 0 and 2 (test_ntt.cu:219-229) ---------------
 @pytest.mark.parametrize("log_rate,log_hs", [(0, range(1, 25)), (2, range(1, 23))])
-def test_golden_md5_gf32(b2, oracle, cuda, log_rate, log_hs):
+def test_golden_md5_gf32(b2, oracle, cuda, log_rate, log_hs, schedule):
     for log_h in log_hs:
         x = oracle.reference_input(log_h, log_rate)
         plan = b2.Plan(32, log_h, log_rate)
@@ -41,10 +41,21 @@ def test_golden_md5_gf32_large(b2, oracle, cuda, log_rate, log_h):
     plan.close()
 
 
+@pytest.fixture(params=["auto", "tile", "bundle"])
+def schedule(request, monkeypatch):
+    """the plan picks its pass schedule by size (b2ntt_plan_create); B2NTT_UPPER pins it, so that the upper/tile kernels and
+    the bundle-pass kernel each meet every small edge case on the GPU"""
+    if request.param != "auto":
+        monkeypatch.setenv("B2NTT_UPPER", "2" if request.param == "tile" else "0")
+    else:
+        monkeypatch.delenv("B2NTT_UPPER", raising=False)
+    return request.param
+
+
 # ---- oracle parity on random inputs, every log_rate, both fields, device-resident path ------------
 @pytest.mark.parametrize("field_bits", [32, 128])
 @pytest.mark.parametrize("log_rate", [0, 1, 2, 3, 4])
-def test_oracle_parity(b2, oracle, cuda, field_bits, log_rate):
+def test_oracle_parity(b2, oracle, cuda, field_bits, log_rate, schedule):
     limbs = field_bits // 32
     for log_h in [1, 2, 3, 4, 5, 6, 7, 9, 12, 15, 16, 18]:
         x = _rand((1 << log_h) * limbs, 1000 * log_h + log_rate)
@@ -55,7 +66,7 @@ def test_oracle_parity(b2, oracle, cuda, field_bits, log_rate):
         plan.close()
 
 
-def test_gf128_limb0_is_golden(b2, oracle, cuda):
+def test_gf128_limb0_is_golden(b2, oracle, cuda, schedule):
     """limb 0 of a GF(2^128) transform fed with the reference stream reproduces the
     GF(2^32) golden digest."""
     for log_h, log_rate in [(20, 0), (18, 2), (22, 0)]:
@@ -69,7 +80,7 @@ def test_gf128_limb0_is_golden(b2, oracle, cuda):
 
 
 @pytest.mark.parametrize("field_bits", [32, 128])
-def test_batch_columns(b2, oracle, cuda, field_bits):
+def test_batch_columns(b2, oracle, cuda, field_bits, schedule):
     limbs = field_bits // 32
     log_h, log_rate, batch = 11, 2, 5
     x = _rand(batch * (1 << log_h) * limbs, 77)
@@ -81,7 +92,7 @@ def test_batch_columns(b2, oracle, cuda, field_bits):
 
 
 @pytest.mark.parametrize("field_bits", [32, 128])
-def test_inverse_roundtrip_and_oracle(b2, oracle, cuda, field_bits):
+def test_inverse_roundtrip_and_oracle(b2, oracle, cuda, field_bits, schedule):
     limbs = field_bits // 32
     for log_h, log_rate in [(3, 0), (10, 0), (14, 2), (20, 1)]:
         x = _rand((1 << log_h) * limbs, log_h)
@@ -97,7 +108,7 @@ def test_inverse_roundtrip_and_oracle(b2, oracle, cuda, field_bits):
 
 
 @pytest.mark.parametrize("field_bits", [32, 128])
-def test_bitsliced_layout(b2, oracle, cuda, field_bits):
+def test_bitsliced_layout(b2, oracle, cuda, field_bits, schedule):
     limbs = field_bits // 32
     for log_h, log_rate in [(5, 0), (6, 1), (8, 0), (13, 2), (17, 0)]:
         x = _rand((1 << log_h) * limbs, 31 * log_h)
@@ -149,7 +160,7 @@ def test_headline_size_properties_gf128(b2, oracle, cuda):
     plan.close()
 
 
-def test_config2_compact_and_bitsliced_agree(b2, oracle, cuda):
+def test_config2_compact_and_bitsliced_agree(b2, oracle, cuda, schedule):
     """config 2: log_n = 24 GF(2^128), the bit-sliced image transforms to the bit-sliced image of the compact result"""
     import torch
 
