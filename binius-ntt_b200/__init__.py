@@ -11,6 +11,7 @@ from .api import (  # noqa: F401
     AdditiveNTTConf,
     DataOrder,
     NTTData,
+    GeneralNTT,
     Plan,
     Sumcheck,
     bitslice_,

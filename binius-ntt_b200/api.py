@@ -57,6 +57,10 @@ def lib():
         L.b2ntt_sumcheck_next_round.argtypes = [vp, vp]
         L.b2ntt_sumcheck_round.argtypes = [vp]
         L.b2ntt_sumcheck_launches.argtypes = [vp]
+        L.b2ntt_general_create.argtypes = [C.POINTER(vp), i, vp, i]
+        L.b2ntt_general_destroy.argtypes = [vp]
+        L.b2ntt_general_exec.argtypes = [vp, vp, vp, i, vp]
+        L.b2ntt_general_constants.argtypes = [vp, vp]
         L.b2ntt_sumcheck_launches.restype = C.c_longlong
         L.b2ntt_strerror.argtypes = [i]
         L.b2ntt_strerror.restype = C.c_char_p
@@ -283,6 +287,46 @@ class AdditiveNTT:
         out.order = DataOrder.IN_ORDER
         self.plan.exec_host(inp.data, out.data)
         return True
+
+
+class GeneralNTT:
+    """b2ntt_general: GF(2^128) additive NTT on a caller-supplied basis (generalises
+    AdditiveNTT<T,P>, ntt/additive_ntt.cuh:176-309, whose basis is fixed to 1 << i).  basis: [log_h, 4] uint32 or None."""
+
+    def __init__(self, log_h, basis=None, device=0):
+        self._h = C.c_void_p()
+        ptr = None
+        if basis is not None:
+            self._basis = np.ascontiguousarray(basis, dtype=np.uint32).reshape(-1)
+            if self._basis.size != 4 * log_h:
+                raise ValueError("basis: expected log_h x 4 words")
+            ptr = self._basis.ctypes.data
+        _check(lib().b2ntt_general_create(C.byref(self._h), log_h, ptr, device), "b2ntt_general_create")
+        self.log_h, self.device, self.words = log_h, device, 4 << log_h
+
+    def close(self):
+        if self._h:
+            lib().b2ntt_general_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def constants(self):
+        out = np.zeros((self.log_h, self.log_h, 4), dtype=np.uint32)
+        _check(lib().b2ntt_general_constants(self._h, out.ctypes.data), "b2ntt_general_constants")
+        return out
+
+    def exec(self, d_in, d_out=None, inverse=False, stream=None):
+        Plan._dev_ok(self, d_in, self.words, "d_in")
+        if d_out is None:
+            d_out = d_in
+        Plan._dev_ok(self, d_out, self.words, "d_out")
+        _check(lib().b2ntt_general_exec(self._h, d_in.data_ptr(), d_out.data_ptr(), int(inverse), _stream_ptr(stream)), "b2ntt_general_exec")
+        return d_out
 
 
 class Sumcheck:

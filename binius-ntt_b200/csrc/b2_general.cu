@@ -1,0 +1,159 @@
+// b2_general.cu -- additive NTT over GF(2^128) on a caller-supplied basis.  sm_100a only.
+//
+// The reference's transform (ntt/additive_ntt.cuh:91-160, :273-309) fixes the basis beta_i = 1 << i, so every twiddle
+// lies in GF(2^32) and log_h + log_rate <= 32.  Here beta_0 .. beta_{log_h-1} are arbitrary GF(2^128) elements, linearly
+// independent over GF(2): the domain constants C[i][j] = W^_i(beta_{i+1+j}) are full-width (same recurrence as
+// precompute_subspace_evals with norm_0 = beta_0 instead of 1) and the butterfly u ^= w * v; v ^= u needs a true
+// GF(2^128) product (b2::gf128_mul, the tower of sumcheck/test/utils/tower_7_mul.cu:4-20).
+//
+// First correct path: one launch per layer, one butterfly per thread, scalar table-free product in registers.  The
+// default basis reproduces b2ntt_exec bit for bit (tests), which is the faster route whenever the basis is 1 << i.
+#include <cuda_runtime.h>
+
+#include <new>
+#include <vector>
+
+#include "../../include/b2ntt.h"
+#include "b2_field.cuh"
+#include "b2_launch.h"
+
+using namespace b2;
+
+namespace {
+
+gf128 g_xor(const gf128& a, const gf128& b) {
+	gf128 r;
+	for (int l = 0; l < 4; l++) r.w[l] = a.w[l] ^ b.w[l];
+	return r;
+}
+bool g_zero(const gf128& a) { return !(a.w[0] | a.w[1] | a.w[2] | a.w[3]); }
+// inverse through the norm to GF(2^64) (finite_fields/binary_tower.cuh:70-80 one level up); inverse(0) = 0
+gf128 g_inverse(const gf128& a) {
+	const uint64_t a0 = a.w[0] | (uint64_t)a.w[1] << 32, a1 = a.w[2] | (uint64_t)a.w[3] << 32;
+	const uint64_t inter = a0 ^ Tower<6>::mul_alpha(a1);
+	const uint64_t delta = gf64_mul(a0, inter) ^ Tower<6>::square(a1);
+	const uint64_t dinv = Tower<6>::inverse(delta);
+	const uint64_t lo = gf64_mul(dinv, inter), hi = gf64_mul(dinv, a1);
+	gf128 r;
+	r.w[0] = (uint32_t)lo, r.w[1] = (uint32_t)(lo >> 32), r.w[2] = (uint32_t)hi, r.w[3] = (uint32_t)(hi >> 32);
+	return r;
+}
+
+constexpr int kMaxLog = 34;  // 2^34 elements = 256 GiB: beyond one B200, the bound only sizes the shared table
+
+// one layer: butterflies t = (block j, offset k), u = j << (layer + 1) | k, v = u | 1 << layer (additive_ntt.cuh:21-33);
+// twiddle = XOR of row[b] over the set bits b of j (calculate_twiddle, :59-77, with full-width constants)
+template <bool INV>
+__global__ void __launch_bounds__(256) general_layer_kernel(uint4* __restrict__ data, const uint4* __restrict__ row, int layer, int nbits, uint64_t n_half) {
+	__shared__ uint4 sc[kMaxLog];
+	if ((int)threadIdx.x < nbits) sc[threadIdx.x] = row[threadIdx.x];
+	__syncthreads();
+	const uint64_t step = (uint64_t)gridDim.x * blockDim.x, kmask = (uint64_t(1) << layer) - 1;
+	for (uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n_half; t += step) {
+		const uint64_t j = t >> layer, ui = (j << (layer + 1)) | (t & kmask), vi = ui | (uint64_t(1) << layer);
+		gf128 w = {{0, 0, 0, 0}};
+		for (int b = 0; b < nbits; b++)
+			if ((j >> b) & 1) {
+				const uint4 c = sc[b];
+				w.w[0] ^= c.x, w.w[1] ^= c.y, w.w[2] ^= c.z, w.w[3] ^= c.w;
+			}
+		uint4 u = data[ui], v = data[vi];
+		if (INV) v.x ^= u.x, v.y ^= u.y, v.z ^= u.z, v.w ^= u.w;
+		const gf128 vv = {{v.x, v.y, v.z, v.w}};
+		const gf128 p = gf128_mul(w, vv);
+		u.x ^= p.w[0], u.y ^= p.w[1], u.z ^= p.w[2], u.w ^= p.w[3];
+		if (!INV) v.x ^= u.x, v.y ^= u.y, v.z ^= u.z, v.w ^= u.w;
+		data[ui] = u, data[vi] = v;
+	}
+}
+
+}  // namespace
+
+struct b2ntt_general {
+	int log_h = 0, device = 0, sms = 0;
+	std::vector<gf128> C;  // [log_h][log_h], row i holds log_h - 1 - i constants
+	uint4* d_C = nullptr;
+};
+
+extern "C" int b2ntt_general_create(b2ntt_general** out, int log_h, const uint32_t* h_basis, int device) {
+	if (!out) return B2NTT_EINVAL;
+	*out = nullptr;
+	if (log_h < 1 || log_h > kMaxLog) return B2NTT_EINVAL;
+	if (!h_basis && log_h > 32) return B2NTT_EINVAL;  // the default basis 1 << i has 32 independent elements in limb 0
+	// unnormalised E_i(beta_k), k >= i: E_0(x) = x, E_i(x) = E_{i-1}(x)^2 + E_{i-1}(beta_{i-1}) * E_{i-1}(x)
+	std::vector<gf128> cur(log_h), C((size_t)log_h * log_h, gf128{{0, 0, 0, 0}});
+	for (int k = 0; k < log_h; k++) {
+		if (h_basis)
+			for (int l = 0; l < 4; l++) cur[k].w[l] = h_basis[4 * k + l];
+		else
+			cur[k] = gf128{{uint32_t(1) << k, 0, 0, 0}};
+	}
+	for (int i = 0; i < log_h; i++) {
+		if (i > 0) {
+			const gf128 np = cur[i - 1];
+			for (int k = i; k < log_h; k++) cur[k] = g_xor(gf128_mul(cur[k], cur[k]), gf128_mul(np, cur[k]));
+		}
+		if (g_zero(cur[i])) return B2NTT_EINVAL;  // beta_i lies in the span of beta_0..beta_{i-1}
+		const gf128 inv = g_inverse(cur[i]);
+		for (int k = i + 1; k < log_h; k++) C[(size_t)i * log_h + (k - i - 1)] = gf128_mul(inv, cur[k]);
+	}
+	int count = 0;
+	if (cudaGetDeviceCount(&count) != cudaSuccess || device < 0 || device >= count) return report_cuda_error(cudaErrorNoDevice, "b2ntt_general_create");
+	b2ntt_general* g = new (std::nothrow) b2ntt_general;
+	if (!g) return B2NTT_ENOMEM;
+	g->log_h = log_h, g->device = device, g->C.swap(C);
+	cudaSetDevice(device);
+	cudaDeviceGetAttribute(&g->sms, cudaDevAttrMultiProcessorCount, device);
+	const size_t bytes = g->C.size() * sizeof(gf128);
+	if (cudaMalloc(&g->d_C, bytes) != cudaSuccess) {
+		delete g;
+		return B2NTT_ENOMEM;
+	}
+	cudaError_t e = cudaMemcpy(g->d_C, g->C.data(), bytes, cudaMemcpyHostToDevice);
+	if (e != cudaSuccess) {
+		cudaFree(g->d_C);
+		delete g;
+		return report_cuda_error(e, "b2ntt_general_create");
+	}
+	*out = g;
+	return B2NTT_OK;
+}
+
+extern "C" int b2ntt_general_destroy(b2ntt_general* g) {
+	if (!g) return B2NTT_OK;
+	cudaSetDevice(g->device);
+	cudaFree(g->d_C);
+	delete g;
+	return B2NTT_OK;
+}
+
+extern "C" int b2ntt_general_constants(const b2ntt_general* g, uint32_t* h_out) {
+	if (!g || !h_out) return B2NTT_EINVAL;
+	for (size_t i = 0; i < g->C.size(); i++)
+		for (int l = 0; l < 4; l++) h_out[4 * i + l] = g->C[i].w[l];
+	return B2NTT_OK;
+}
+
+extern "C" int b2ntt_general_exec(b2ntt_general* g, const void* d_in, void* d_out, int inverse, void* stream) {
+	if (!g || !d_in || !d_out) return B2NTT_EINVAL;
+	cudaStream_t st = (cudaStream_t)stream;
+	cudaSetDevice(g->device);
+	const uint64_t n = uint64_t(1) << g->log_h, n_half = n >> 1;
+	if (d_in != d_out) {
+		cudaError_t e = cudaMemcpyAsync(d_out, d_in, n * sizeof(gf128), cudaMemcpyDeviceToDevice, st);
+		if (e != cudaSuccess) return report_cuda_error(e, "b2ntt_general_exec copy");
+	}
+	const uint64_t want = (n_half + 255) / 256, cap = (uint64_t)g->sms * 8 * 4;
+	const unsigned grid = (unsigned)(want < cap ? want : cap);
+	for (int s = 0; s < g->log_h; s++) {
+		const int layer = inverse ? s : g->log_h - 1 - s;  // forward runs the widest stride first (additive_ntt.cuh:233-247)
+		const uint4* row = g->d_C + (size_t)layer * g->log_h;
+		const int nbits = g->log_h - 1 - layer;
+		if (inverse)
+			general_layer_kernel<true><<<grid, 256, 0, st>>>((uint4*)d_out, row, layer, nbits, n_half);
+		else
+			general_layer_kernel<false><<<grid, 256, 0, st>>>((uint4*)d_out, row, layer, nbits, n_half);
+	}
+	cudaError_t e = cudaGetLastError();
+	return e == cudaSuccess ? B2NTT_OK : report_cuda_error(e, "b2ntt_general_exec");
+}

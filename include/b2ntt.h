@@ -147,6 +147,22 @@ int b2ntt_sumcheck_next_round(b2ntt_sumcheck* sc, const uint32_t* challenge);
 int b2ntt_sumcheck_round(const b2ntt_sumcheck* sc);
 long long b2ntt_sumcheck_launches(const b2ntt_sumcheck* sc);
 
+/* ---- additive NTT over GF(2^128) on a caller-supplied basis (full-width twiddles / general domains) ----
+ * Generalises AdditiveNTT<T,P> (ntt/additive_ntt.cuh:176-309), whose basis is fixed to beta_i = 1 << i (:281-283) and whose
+ * twiddles therefore stay in GF(2^32).  h_basis = log_h elements of four little-endian limbs, linearly independent over
+ * GF(2) (B2NTT_EINVAL otherwise); NULL = the reference basis, for which the output equals b2ntt_exec's (log_h <= 32).
+ * Input = novel-basis coefficients in natural order, output = evaluations, point i = XOR of beta_b over the set bits b of
+ * i (additive_ntt.cuh:250-259).  1 <= log_h <= 34; log_rate is not separate here: a rate-1/R code is a log_h + log R basis
+ * with zero-padded input. */
+typedef struct b2ntt_general b2ntt_general;
+int b2ntt_general_create(b2ntt_general** g, int log_h, const uint32_t* h_basis, int device);
+int b2ntt_general_destroy(b2ntt_general* g);
+/* d_in / d_out: 2^log_h compact GF(2^128) elements on the device (may alias); inverse != 0 runs evaluations -> coefficients. */
+int b2ntt_general_exec(b2ntt_general* g, const void* d_in, void* d_out, int inverse, void* stream);
+/* The normalised domain constants W^_i(beta_{i+1+j}) (precompute_subspace_evals, additive_ntt.cuh:273-309), row-major
+ * [log_h][log_h] elements of 4 words, row i holding log_h - 1 - i entries (rest zero). */
+int b2ntt_general_constants(const b2ntt_general* g, uint32_t* h_out);
+
 const char* b2ntt_strerror(int code);
 /* Text of the last CUDA error seen by the calling thread's last failing call ("" if none). */
 const char* b2ntt_last_cuda_error(void);

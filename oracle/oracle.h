@@ -78,6 +78,12 @@ int orc_antt_forward_full128(const uint32_t* in, uint32_t* out, int log_h, int l
 int orc_antt_inverse(const uint32_t* in, uint32_t* out, int log_h, int log_rate, int coset, int limbs,
                      int threads);
 
+
+/* ---- general-basis GF(2^128) additive NTT (antt_general.c) ---- */
+int orc_antt_general_constants(int log_h, const uint32_t* basis /* log_h * 4 or NULL */, uint32_t* C /* log_h*log_h*4 */);
+int orc_antt_general(const uint32_t* in, uint32_t* out, int log_h, const uint32_t* basis, int inverse);
+int orc_antt_general_direct(const uint32_t* in, uint32_t* out, int log_h, const uint32_t* basis);
+
 /* ---- MD5 (ntt/tests/md5.cu; RFC 1321) and the reference's test-vector stream ---- */
 void orc_md5(const void* data, size_t len, uint8_t digest[16]);
 void orc_md5_hex(const void* data, size_t len, char hex[33]);

@@ -51,6 +51,12 @@ def _load():
     lib.orc_antt_inverse.argtypes = [_u32p, _u32p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
     lib.orc_antt_inverse.restype = C.c_int
     lib.orc_antt_set_plain.argtypes = [C.c_int]
+    lib.orc_antt_general_constants.argtypes = [C.c_int, C.c_void_p, _u32p]
+    lib.orc_antt_general_constants.restype = C.c_int
+    lib.orc_antt_general.argtypes = [_u32p, _u32p, C.c_int, C.c_void_p, C.c_int]
+    lib.orc_antt_general.restype = C.c_int
+    lib.orc_antt_general_direct.argtypes = [_u32p, _u32p, C.c_int, C.c_void_p]
+    lib.orc_antt_general_direct.restype = C.c_int
     lib.orc_md5_hex.argtypes = [C.c_void_p, C.c_size_t, C.c_char_p]
     lib.orc_mt19937_fill.argtypes = [C.c_uint32, _u32p, C.c_size_t]
     lib.orc_golden_md5.argtypes = [C.c_int, C.c_int]
@@ -144,6 +150,36 @@ def antt_forward_full128(x, log_h, log_rate):
     rc = lib.orc_antt_forward_full128(x, out, log_h, log_rate)
     if rc:
         raise ValueError("bad arguments")
+    return out
+
+
+def _basis_ptr(basis, log_h):
+    if basis is None:
+        return None, None
+    b = np.ascontiguousarray(basis, dtype=np.uint32).reshape(-1)
+    assert b.size == 4 * log_h
+    return b, b.ctypes.data
+
+
+def antt_general_constants(log_h, basis=None):
+    """[log_h, log_h, 4] normalised constants W^_i(beta_{i+1+j}) (antt_general.c)."""
+    keep, ptr = _basis_ptr(basis, log_h)
+    out = np.zeros((log_h, log_h, 4), dtype=np.uint32)
+    if lib.orc_antt_general_constants(log_h, ptr, out.reshape(-1)):
+        raise ValueError("linearly dependent basis")
+    return out
+
+
+def antt_general(x, log_h, basis=None, inverse=False, direct=False):
+    """GF(2^128) additive NTT on the basis `basis` (log_h x 4 words; None = 1 << i).  direct=True evaluates the
+    definition instead of the butterfly network (log_h <= 8)."""
+    x = np.ascontiguousarray(x, dtype=np.uint32).reshape(-1)
+    assert x.size == 4 << log_h
+    keep, ptr = _basis_ptr(basis, log_h)
+    out = np.empty_like(x)
+    rc = lib.orc_antt_general_direct(x, out, log_h, ptr) if direct else lib.orc_antt_general(x, out, log_h, ptr, int(inverse))
+    if rc:
+        raise ValueError("bad arguments or linearly dependent basis")
     return out
 
 
