@@ -6,8 +6,11 @@
 // precompute_subspace_evals with norm_0 = beta_0 instead of 1) and the butterfly u ^= w * v; v ^= u needs a true
 // GF(2^128) product (b2::gf128_mul, the tower of sumcheck/test/utils/tower_7_mul.cu:4-20).
 //
-// First correct path: one launch per layer, one butterfly per thread, scalar table-free product in registers.  The
-// default basis reproduces b2ntt_exec bit for bit (tests), which is the faster route whenever the basis is 1 << i.
+// One launch per layer.  From log_h = 11 up a CTA takes 1024 butterflies per iteration: it stages the V operands and the
+// 1024 twiddles (compact), bit-slices both in shared memory, multiplies with the CTA-level product of b2_mul128.cuh (the
+// one behind b2ntt_mul and the sumcheck kernels), transposes the products back and applies the XORs on the way out.
+// Below that size: one butterfly per thread with the scalar table-free product.  The default basis reproduces b2ntt_exec
+// bit for bit (tests), which is the faster route whenever the basis is 1 << i.
 #include <cuda_runtime.h>
 
 #include <new>
@@ -16,6 +19,7 @@
 #include "../../include/b2ntt.h"
 #include "b2_field.cuh"
 #include "b2_launch.h"
+#include "b2_mul128.cuh"
 
 using namespace b2;
 
@@ -67,6 +71,77 @@ __global__ void __launch_bounds__(256) general_layer_kernel(uint4* __restrict__ 
 	}
 }
 
+// 1024 butterflies per CTA iteration (n_half is a multiple of 1024).  Chunk ch of the iteration = butterfly t = 1024 c + ch,
+// staged as 16-byte element (ch & 31) of block row ch >> 5, the image mul_sliced128_kernel<true> (b2_misc.cu) works on.
+template <bool INV>
+__global__ void __launch_bounds__(kMulThreads, 2) general_layer_cta_kernel(uint4* __restrict__ data, const uint4* __restrict__ row, int layer, int nbits, uint64_t n_half) {
+	extern __shared__ __align__(16) uint32_t gsm[];
+	const MulSmem m = mul_smem_view(gsm);
+	uint32_t *sa = m.sa, *sb = m.sb;
+	uint4* sc = reinterpret_cast<uint4*>(gsm + kMulSmemWords);
+	const int j = threadIdx.x >> 5, lb = threadIdx.x & 31;
+	if ((int)threadIdx.x < nbits) sc[threadIdx.x] = row[threadIdx.x];
+	__syncthreads();
+	const uint64_t kmask = (uint64_t(1) << layer) - 1;
+	for (uint64_t t0 = (uint64_t)blockIdx.x * 1024; t0 < n_half; t0 += (uint64_t)gridDim.x * 1024) {
+		for (int ch = threadIdx.x; ch < 1024; ch += kMulThreads) {
+			const uint64_t t = t0 + ch, blk = t >> layer, ui = (blk << (layer + 1)) | (t & kmask), vi = ui | (uint64_t(1) << layer);
+			uint4 v = data[vi];
+			if (INV) {
+				const uint4 u = data[ui];
+				v.x ^= u.x, v.y ^= u.y, v.z ^= u.z, v.w ^= u.w;
+			}
+			uint4 w = make_uint4(0, 0, 0, 0);
+			for (int b = 0; b < nbits; b++)
+				if ((blk >> b) & 1) {
+					const uint4 c = sc[b];
+					w.x ^= c.x, w.y ^= c.y, w.z ^= c.z, w.w ^= c.w;
+				}
+			const int off = (ch >> 5) * kMulPitch + (ch & 31) * 4;
+			*reinterpret_cast<uint4*>(sa + off) = v;
+			*reinterpret_cast<uint4*>(sb + off) = w;
+		}
+		__syncthreads();
+		if (j < 8) {  // compact -> bit-sliced, both operands (lane = 4 * block + limb)
+			uint32_t r[32];
+			uint32_t* rw = (j < 4 ? sa : sb) + (8 * (j & 3) + (lb >> 2)) * kMulPitch;
+			const int k = lb & 3;
+#pragma unroll
+			for (int e = 0; e < 32; e++) r[e] = rw[4 * e + k];
+			transpose32(r);
+			__syncwarp();
+#pragma unroll
+			for (int i = 0; i < 32; i++) rw[32 * k + i] = r[i];
+		}
+		__syncthreads();
+		cta_mul128(sa, sb, m.sp, m.sz, 32);
+		if (j < 4) {  // products back to compact
+			uint32_t r[32];
+			uint32_t* rw = sa + (8 * j + (lb >> 2)) * kMulPitch;
+			const int k = lb & 3;
+#pragma unroll
+			for (int i = 0; i < 32; i++) r[i] = rw[32 * k + i];
+			transpose32(r);
+			__syncwarp();
+#pragma unroll
+			for (int e = 0; e < 32; e++) rw[4 * e + k] = r[e];
+		}
+		__syncthreads();
+		for (int ch = threadIdx.x; ch < 1024; ch += kMulThreads) {
+			const uint64_t t = t0 + ch, blk = t >> layer, ui = (blk << (layer + 1)) | (t & kmask), vi = ui | (uint64_t(1) << layer);
+			const uint4 p = *reinterpret_cast<const uint4*>(sa + (ch >> 5) * kMulPitch + (ch & 31) * 4);
+			uint4 u = data[ui], v = data[vi];  // second read of the pair: L2-resident, this CTA fetched it a few microseconds ago
+			if (INV) v.x ^= u.x, v.y ^= u.y, v.z ^= u.z, v.w ^= u.w;
+			u.x ^= p.x, u.y ^= p.y, u.z ^= p.z, u.w ^= p.w;
+			if (!INV) v.x ^= u.x, v.y ^= u.y, v.z ^= u.z, v.w ^= u.w;
+			data[ui] = u, data[vi] = v;
+		}
+		__syncthreads();
+	}
+}
+
+constexpr size_t kGeneralSmemBytes = kMulSmemBytes + kMaxLog * sizeof(uint4);
+
 }  // namespace
 
 struct b2ntt_general {
@@ -104,6 +179,8 @@ extern "C" int b2ntt_general_create(b2ntt_general** out, int log_h, const uint32
 	g->log_h = log_h, g->device = device, g->C.swap(C);
 	cudaSetDevice(device);
 	cudaDeviceGetAttribute(&g->sms, cudaDevAttrMultiProcessorCount, device);
+	cudaFuncSetAttribute(general_layer_cta_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGeneralSmemBytes);
+	cudaFuncSetAttribute(general_layer_cta_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGeneralSmemBytes);
 	const size_t bytes = g->C.size() * sizeof(gf128);
 	if (cudaMalloc(&g->d_C, bytes) != cudaSuccess) {
 		delete g;
@@ -145,11 +222,18 @@ extern "C" int b2ntt_general_exec(b2ntt_general* g, const void* d_in, void* d_ou
 	}
 	const uint64_t want = (n_half + 255) / 256, cap = (uint64_t)g->sms * 8 * 4;
 	const unsigned grid = (unsigned)(want < cap ? want : cap);
+	const bool cta = g->log_h >= 11;
+	const uint64_t cta_want = n_half / 1024, cta_cap = (uint64_t)g->sms * 2;
+	const unsigned cta_grid = (unsigned)(cta_want < cta_cap ? cta_want : cta_cap);
 	for (int s = 0; s < g->log_h; s++) {
 		const int layer = inverse ? s : g->log_h - 1 - s;  // forward runs the widest stride first (additive_ntt.cuh:233-247)
 		const uint4* row = g->d_C + (size_t)layer * g->log_h;
 		const int nbits = g->log_h - 1 - layer;
-		if (inverse)
+		if (cta && inverse)
+			general_layer_cta_kernel<true><<<cta_grid, kMulThreads, kGeneralSmemBytes, st>>>((uint4*)d_out, row, layer, nbits, n_half);
+		else if (cta)
+			general_layer_cta_kernel<false><<<cta_grid, kMulThreads, kGeneralSmemBytes, st>>>((uint4*)d_out, row, layer, nbits, n_half);
+		else if (inverse)
 			general_layer_kernel<true><<<grid, 256, 0, st>>>((uint4*)d_out, row, layer, nbits, n_half);
 		else
 			general_layer_kernel<false><<<grid, 256, 0, st>>>((uint4*)d_out, row, layer, nbits, n_half);

@@ -87,7 +87,7 @@ def _host(t):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("log_h", [1, 2, 3, 6, 9, 13, 16])
+@pytest.mark.parametrize("log_h", [1, 2, 3, 6, 9, 10, 11, 12, 13, 16])  # 11 = first size on the CTA-level product
 def test_gpu_general_vs_oracle(b2, oracle, cuda, log_h):
     basis = _basis(log_h, 40 + log_h)
     g = b2.GeneralNTT(log_h, basis)
