@@ -49,3 +49,40 @@ private:
 	AdditiveNTTConf<T, P> ntt_conf;
 	b2ntt_plan* plan = nullptr;
 };
+
+// GF(2^128) transform on a caller-supplied basis (no reference counterpart: additive_ntt.cuh:281-283 fixes
+// beta_i = 1 << i).  Same apply() contract as AdditiveNTT with log_rate = 0, plus the inverse; basis = nullptr is the
+// reference basis and gives AdditiveNTT<b128, FanPaarTowerField<7>>'s output word for word.
+class GeneralAdditiveNTT {
+public:
+	GeneralAdditiveNTT(int log_h, const b128* basis) : log_h(log_h) {
+		const int rc = b2ntt_general_create(&g, log_h, reinterpret_cast<const uint32_t*>(basis), 0);
+		if (rc != B2NTT_OK) {
+			std::cerr << "GeneralAdditiveNTT: " << b2ntt_strerror(rc) << " " << b2ntt_last_cuda_error() << std::endl;
+			g = nullptr;
+		}
+	}
+	GeneralAdditiveNTT(const GeneralAdditiveNTT&) = delete;
+	GeneralAdditiveNTT& operator=(const GeneralAdditiveNTT&) = delete;
+	~GeneralAdditiveNTT() { b2ntt_general_destroy(g); }
+	bool valid() const { return g != nullptr; }
+
+	bool apply(const NTTData<b128>& input, NTTData<b128>& output, bool inverse = false) {
+		if (!g || input.size != ((size_t)1 << log_h) || input.order != DataOrder::IN_ORDER) return false;
+		const size_t bytes = input.size * sizeof(b128);
+		void* d = nullptr;
+		if (cudaMalloc(&d, bytes) != cudaSuccess) return false;
+		bool ok = cudaMemcpy(d, input.data.get(), bytes, cudaMemcpyHostToDevice) == cudaSuccess && b2ntt_general_exec(g, d, d, inverse, nullptr) == B2NTT_OK &&
+		          cudaMemcpy(output.data.get(), d, bytes, cudaMemcpyDeviceToHost) == cudaSuccess;
+		cudaFree(d);
+		if (ok) output.order = DataOrder::IN_ORDER;
+		return ok;
+	}
+	bool apply_device(const b128* d_in, b128* d_out, bool inverse = false, cudaStream_t stream = 0) {
+		return g && b2ntt_general_exec(g, d_in, d_out, inverse, (void*)stream) == B2NTT_OK;
+	}
+
+private:
+	int log_h;
+	b2ntt_general* g = nullptr;
+};

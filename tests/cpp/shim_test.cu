@@ -66,6 +66,32 @@ static bool run_and_check_additive_ntt128(int log_h, int log_rate) {
 	return want && strcmp(hex, want) == 0;
 }
 
+// general-basis transform through the C++ shim against the oracle's restatement (oracle/antt_general.c)
+static bool run_and_check_general_ntt(int log_h, bool reference_basis) {
+	std::mt19937 gen(777 + log_h);
+	const size_t n = (size_t)1 << log_h;
+	std::vector<b128> basis(log_h);
+	for (int k = 0; k < log_h; k++)
+		for (int l = 0; l < 4; l++) basis[k].w[l] = gen();  // independent with probability ~ 1 - 2^(log_h - 128)
+	const b128* bp = reference_basis ? nullptr : basis.data();
+	NTTData<b128> in(DataOrder::IN_ORDER, n), out(n), back(n);
+	for (size_t i = 0; i < n; i++)
+		for (int l = 0; l < 4; l++) in.data[i].w[l] = gen();
+	GeneralAdditiveNTT ntt(log_h, bp);
+	if (!ntt.valid() || !ntt.apply(in, out)) return false;
+	std::vector<uint32_t> want(4 * n);
+	if (orc_antt_general(reinterpret_cast<const uint32_t*>(in.data.get()), want.data(), log_h, reinterpret_cast<const uint32_t*>(bp), 0)) return false;
+	if (memcmp(want.data(), out.data.get(), 16 * n)) return false;
+	if (reference_basis) {  // equals the stock class
+		AdditiveNTTConf<b128, FanPaarTowerField<7>> conf(log_h, 0);
+		AdditiveNTT<b128, FanPaarTowerField<7>> stock(conf);
+		NTTData<b128> o2(n);
+		if (!stock.apply(in, o2) || memcmp(o2.data.get(), out.data.get(), 16 * n)) return false;
+	}
+	out.order = DataOrder::IN_ORDER;
+	return ntt.apply(out, back, true) && memcmp(back.data.get(), in.data.get(), 16 * n) == 0;
+}
+
 // sumcheck/test/test.cu:16-96 (test_sumcheck<NUM_VARS, COMPOSITION_SIZE, DATA_IS_TRANSPOSED>) with the verifier of
 // sumcheck/test/verifier.cu restated by the oracle; seeded instead of time-seeded
 template <uint32_t NUM_VARS, uint32_t COMPOSITION_SIZE, bool DATA_IS_TRANSPOSED>
@@ -136,6 +162,14 @@ int main(int argc, char** argv) {
 	for (int log_h = 1; log_h <= max_r2; log_h++) CHECK(run_and_check_additive_ntt(log_h, 2));
 	for (int log_h : {3, 9, 16, 20}) CHECK(run_and_check_additive_ntt128(log_h, 0));
 	CHECK(run_and_check_additive_ntt128(14, 2));
+	for (int log_h : {1, 5, 10, 11, 15}) CHECK(run_and_check_general_ntt(log_h, false));
+	for (int log_h : {4, 12}) CHECK(run_and_check_general_ntt(log_h, true));
+	{  // a dependent basis is refused
+		b128 dep[3] = {};
+		dep[0].w[0] = 5, dep[1].w[2] = 9, dep[2].w[0] = 5, dep[2].w[2] = 9;
+		GeneralAdditiveNTT bad(3, dep);
+		CHECK(!bad.valid());
+	}
 	{  // apply(): false on wrong size / order, nothing else (additive_ntt.cuh:206-208)
 		AdditiveNTTConf<uint32_t, FanPaarTowerField<5>> conf(10, 0);
 		AdditiveNTT<uint32_t, FanPaarTowerField<5>> ntt(conf);
