@@ -6,7 +6,7 @@
 // precompute_subspace_evals with norm_0 = beta_0 instead of 1) and the butterfly u ^= w * v; v ^= u needs a true
 // GF(2^128) product (b2::gf128_mul, the tower of sumcheck/test/utils/tower_7_mul.cu:4-20).
 //
-// One launch per layer.  From log_h = 11 up a CTA takes 1024 butterflies per iteration: it stages the V operands and the
+// From log_h = 11 up: one launch per two layers, a CTA takes 1024 butterflies per layer and iteration: it stages the V operands and the
 // 1024 twiddles (compact), bit-slices both in shared memory, multiplies with the CTA-level product of b2_mul128.cuh (the
 // one behind b2ntt_mul and the sumcheck kernels), transposes the products back and applies the XORs on the way out.
 // Below that size: one butterfly per thread with the scalar table-free product.  The default basis reproduces b2ntt_exec
@@ -71,76 +71,103 @@ __global__ void __launch_bounds__(256) general_layer_kernel(uint4* __restrict__ 
 	}
 }
 
-// 1024 butterflies per CTA iteration (n_half is a multiple of 1024).  Chunk ch of the iteration = butterfly t = 1024 c + ch,
-// staged as 16-byte element (ch & 31) of block row ch >> 5, the image mul_sliced128_kernel<true> (b2_misc.cu) works on.
+// 1024 butterflies per CTA iteration and layer (n_half is a multiple of 1024).  Butterfly ch of the iteration is staged as
+// 16-byte element (ch & 31) of block row ch >> 5, the image mul_sliced128_kernel<true> (b2_misc.cu) works on.
+// nl = 1: one layer `hi`, butterflies t = 1024 * it + ch.  nl = 2: layers hi and hi - 1 on 512 quads of elements that differ
+// in index bits hi and hi - 1 (quad q = 512 * it + (ch & 511), pair ch >> 9 of the quad): the second layer reads what the
+// same CTA wrote a moment earlier (L2/L1, made visible by the CTA barrier), so two layers cost one HBM round trip.
 template <bool INV>
-__global__ void __launch_bounds__(kMulThreads, 2) general_layer_cta_kernel(uint4* __restrict__ data, const uint4* __restrict__ row, int layer, int nbits, uint64_t n_half) {
+__global__ void __launch_bounds__(kMulThreads, 2) general_layer_cta_kernel(uint4* __restrict__ data, const uint4* __restrict__ rows, int log_h, int hi, int nl, uint64_t n_half) {
 	extern __shared__ __align__(16) uint32_t gsm[];
 	const MulSmem m = mul_smem_view(gsm);
 	uint32_t *sa = m.sa, *sb = m.sb;
-	uint4* sc = reinterpret_cast<uint4*>(gsm + kMulSmemWords);
+	uint4* sc = reinterpret_cast<uint4*>(gsm + kMulSmemWords);  // [2][kMaxLog]: constants of layer hi, of layer hi - 1
 	const int j = threadIdx.x >> 5, lb = threadIdx.x & 31;
-	if ((int)threadIdx.x < nbits) sc[threadIdx.x] = row[threadIdx.x];
+	if ((int)threadIdx.x < log_h) {
+		sc[threadIdx.x] = rows[(size_t)hi * log_h + threadIdx.x];
+		if (nl == 2) sc[kMaxLog + threadIdx.x] = rows[(size_t)(hi - 1) * log_h + threadIdx.x];
+	}
 	__syncthreads();
-	const uint64_t kmask = (uint64_t(1) << layer) - 1;
-	for (uint64_t t0 = (uint64_t)blockIdx.x * 1024; t0 < n_half; t0 += (uint64_t)gridDim.x * 1024) {
-		for (int ch = threadIdx.x; ch < 1024; ch += kMulThreads) {
-			const uint64_t t = t0 + ch, blk = t >> layer, ui = (blk << (layer + 1)) | (t & kmask), vi = ui | (uint64_t(1) << layer);
-			uint4 v = data[vi];
-			if (INV) {
-				const uint4 u = data[ui];
-				v.x ^= u.x, v.y ^= u.y, v.z ^= u.z, v.w ^= u.w;
-			}
-			uint4 w = make_uint4(0, 0, 0, 0);
-			for (int b = 0; b < nbits; b++)
-				if ((blk >> b) & 1) {
-					const uint4 c = sc[b];
-					w.x ^= c.x, w.y ^= c.y, w.z ^= c.z, w.w ^= c.w;
+	const uint64_t n_iter = n_half / 1024;  // nl = 2: n / 4 quads, 512 per iteration
+	for (uint64_t it = blockIdx.x; it < n_iter; it += gridDim.x) {
+#pragma unroll 1
+		for (int ph = 0; ph < nl; ph++) {
+			// layer of this phase: forward runs hi first, the inverse hi - 1 first
+			const int layer = nl == 1 ? hi : ((ph == 0) != INV ? hi : hi - 1);
+			const int nbits = log_h - 1 - layer;
+			const uint4* tab = sc + (layer == hi ? 0 : kMaxLog);
+			const uint64_t kmask = (uint64_t(1) << layer) - 1, lowmask = nl == 2 ? (uint64_t(1) << (hi - 1)) - 1 : 0;
+			auto pair = [&](int ch, uint64_t& ui, uint64_t& vi) {
+				if (nl == 1) {
+					const uint64_t t = it * 1024 + ch;
+					ui = ((t >> layer) << (layer + 1)) | (t & kmask);
+				} else {
+					const uint64_t q = it * 512 + (ch & 511), e0 = ((q >> (hi - 1)) << (hi + 1)) | (q & lowmask);
+					ui = e0 | ((uint64_t)(ch >> 9) << (layer == hi ? hi - 1 : hi));
 				}
-			const int off = (ch >> 5) * kMulPitch + (ch & 31) * 4;
-			*reinterpret_cast<uint4*>(sa + off) = v;
-			*reinterpret_cast<uint4*>(sb + off) = w;
-		}
-		__syncthreads();
-		if (j < 8) {  // compact -> bit-sliced, both operands (lane = 4 * block + limb)
-			uint32_t r[32];
-			uint32_t* rw = (j < 4 ? sa : sb) + (8 * (j & 3) + (lb >> 2)) * kMulPitch;
-			const int k = lb & 3;
+				vi = ui | (uint64_t(1) << layer);
+			};
+			for (int ch = threadIdx.x; ch < 1024; ch += kMulThreads) {
+				uint64_t ui, vi;
+				pair(ch, ui, vi);
+				const uint64_t blk = ui >> (layer + 1);
+				uint4 v = data[vi];
+				if (INV) {
+					const uint4 u = data[ui];
+					v.x ^= u.x, v.y ^= u.y, v.z ^= u.z, v.w ^= u.w;
+				}
+				uint4 w = make_uint4(0, 0, 0, 0);
+				for (int b = 0; b < nbits; b++)
+					if ((blk >> b) & 1) {
+						const uint4 c = tab[b];
+						w.x ^= c.x, w.y ^= c.y, w.z ^= c.z, w.w ^= c.w;
+					}
+				const int off = (ch >> 5) * kMulPitch + (ch & 31) * 4;
+				*reinterpret_cast<uint4*>(sa + off) = v;
+				*reinterpret_cast<uint4*>(sb + off) = w;
+			}
+			__syncthreads();
+			if (j < 8) {  // compact -> bit-sliced, both operands (lane = 4 * block + limb)
+				uint32_t r[32];
+				uint32_t* rw = (j < 4 ? sa : sb) + (8 * (j & 3) + (lb >> 2)) * kMulPitch;
+				const int k = lb & 3;
 #pragma unroll
-			for (int e = 0; e < 32; e++) r[e] = rw[4 * e + k];
-			transpose32(r);
-			__syncwarp();
+				for (int e = 0; e < 32; e++) r[e] = rw[4 * e + k];
+				transpose32(r);
+				__syncwarp();
 #pragma unroll
-			for (int i = 0; i < 32; i++) rw[32 * k + i] = r[i];
-		}
-		__syncthreads();
-		cta_mul128(sa, sb, m.sp, m.sz, 32);
-		if (j < 4) {  // products back to compact
-			uint32_t r[32];
-			uint32_t* rw = sa + (8 * j + (lb >> 2)) * kMulPitch;
-			const int k = lb & 3;
+				for (int i = 0; i < 32; i++) rw[32 * k + i] = r[i];
+			}
+			__syncthreads();
+			cta_mul128(sa, sb, m.sp, m.sz, 32);
+			if (j < 4) {  // products back to compact
+				uint32_t r[32];
+				uint32_t* rw = sa + (8 * j + (lb >> 2)) * kMulPitch;
+				const int k = lb & 3;
 #pragma unroll
-			for (int i = 0; i < 32; i++) r[i] = rw[32 * k + i];
-			transpose32(r);
-			__syncwarp();
+				for (int i = 0; i < 32; i++) r[i] = rw[32 * k + i];
+				transpose32(r);
+				__syncwarp();
 #pragma unroll
-			for (int e = 0; e < 32; e++) rw[4 * e + k] = r[e];
+				for (int e = 0; e < 32; e++) rw[4 * e + k] = r[e];
+			}
+			__syncthreads();
+			for (int ch = threadIdx.x; ch < 1024; ch += kMulThreads) {
+				uint64_t ui, vi;
+				pair(ch, ui, vi);
+				const uint4 p = *reinterpret_cast<const uint4*>(sa + (ch >> 5) * kMulPitch + (ch & 31) * 4);
+				uint4 u = data[ui], v = data[vi];  // second read of the pair: L2-resident, this CTA fetched it a few microseconds ago
+				if (INV) v.x ^= u.x, v.y ^= u.y, v.z ^= u.z, v.w ^= u.w;
+				u.x ^= p.x, u.y ^= p.y, u.z ^= p.z, u.w ^= p.w;
+				if (!INV) v.x ^= u.x, v.y ^= u.y, v.z ^= u.z, v.w ^= u.w;
+				data[ui] = u, data[vi] = v;
+			}
+			__syncthreads();  // also publishes this phase's stores to the CTA's next phase
 		}
-		__syncthreads();
-		for (int ch = threadIdx.x; ch < 1024; ch += kMulThreads) {
-			const uint64_t t = t0 + ch, blk = t >> layer, ui = (blk << (layer + 1)) | (t & kmask), vi = ui | (uint64_t(1) << layer);
-			const uint4 p = *reinterpret_cast<const uint4*>(sa + (ch >> 5) * kMulPitch + (ch & 31) * 4);
-			uint4 u = data[ui], v = data[vi];  // second read of the pair: L2-resident, this CTA fetched it a few microseconds ago
-			if (INV) v.x ^= u.x, v.y ^= u.y, v.z ^= u.z, v.w ^= u.w;
-			u.x ^= p.x, u.y ^= p.y, u.z ^= p.z, u.w ^= p.w;
-			if (!INV) v.x ^= u.x, v.y ^= u.y, v.z ^= u.z, v.w ^= u.w;
-			data[ui] = u, data[vi] = v;
-		}
-		__syncthreads();
 	}
 }
 
-constexpr size_t kGeneralSmemBytes = kMulSmemBytes + kMaxLog * sizeof(uint4);
+constexpr size_t kGeneralSmemBytes = kMulSmemBytes + 2 * kMaxLog * sizeof(uint4);
 
 }  // namespace
 
@@ -220,23 +247,34 @@ extern "C" int b2ntt_general_exec(b2ntt_general* g, const void* d_in, void* d_ou
 		cudaError_t e = cudaMemcpyAsync(d_out, d_in, n * sizeof(gf128), cudaMemcpyDeviceToDevice, st);
 		if (e != cudaSuccess) return report_cuda_error(e, "b2ntt_general_exec copy");
 	}
-	const uint64_t want = (n_half + 255) / 256, cap = (uint64_t)g->sms * 8 * 4;
-	const unsigned grid = (unsigned)(want < cap ? want : cap);
-	const bool cta = g->log_h >= 11;
-	const uint64_t cta_want = n_half / 1024, cta_cap = (uint64_t)g->sms * 2;
-	const unsigned cta_grid = (unsigned)(cta_want < cta_cap ? cta_want : cta_cap);
-	for (int s = 0; s < g->log_h; s++) {
-		const int layer = inverse ? s : g->log_h - 1 - s;  // forward runs the widest stride first (additive_ntt.cuh:233-247)
-		const uint4* row = g->d_C + (size_t)layer * g->log_h;
-		const int nbits = g->log_h - 1 - layer;
-		if (cta && inverse)
-			general_layer_cta_kernel<true><<<cta_grid, kMulThreads, kGeneralSmemBytes, st>>>((uint4*)d_out, row, layer, nbits, n_half);
-		else if (cta)
-			general_layer_cta_kernel<false><<<cta_grid, kMulThreads, kGeneralSmemBytes, st>>>((uint4*)d_out, row, layer, nbits, n_half);
-		else if (inverse)
-			general_layer_kernel<true><<<grid, 256, 0, st>>>((uint4*)d_out, row, layer, nbits, n_half);
-		else
-			general_layer_kernel<false><<<grid, 256, 0, st>>>((uint4*)d_out, row, layer, nbits, n_half);
+	if (g->log_h >= 11) {
+		// layers in pairs (hi, hi - 1), one launch each; an odd layer count leaves one single-layer launch
+		const uint64_t cap = (uint64_t)g->sms * 2;
+		int done = 0;
+		while (done < g->log_h) {
+			const int nl = g->log_h - done >= 2 ? 2 : 1;
+			// forward walks the strides down (additive_ntt.cuh:233-247), the inverse up
+			const int hi = inverse ? done + nl - 1 : g->log_h - 1 - done;
+			const uint64_t want = n_half / 1024;
+			const unsigned grid = (unsigned)(want < cap ? want : cap);
+			if (inverse)
+				general_layer_cta_kernel<true><<<grid, kMulThreads, kGeneralSmemBytes, st>>>((uint4*)d_out, g->d_C, g->log_h, hi, nl, n_half);
+			else
+				general_layer_cta_kernel<false><<<grid, kMulThreads, kGeneralSmemBytes, st>>>((uint4*)d_out, g->d_C, g->log_h, hi, nl, n_half);
+			done += nl;
+		}
+	} else {
+		const uint64_t want = (n_half + 255) / 256, cap = (uint64_t)g->sms * 8 * 4;
+		const unsigned grid = (unsigned)(want < cap ? want : cap);
+		for (int s = 0; s < g->log_h; s++) {
+			const int layer = inverse ? s : g->log_h - 1 - s;
+			const uint4* row = g->d_C + (size_t)layer * g->log_h;
+			const int nbits = g->log_h - 1 - layer;
+			if (inverse)
+				general_layer_kernel<true><<<grid, 256, 0, st>>>((uint4*)d_out, row, layer, nbits, n_half);
+			else
+				general_layer_kernel<false><<<grid, 256, 0, st>>>((uint4*)d_out, row, layer, nbits, n_half);
+		}
 	}
 	cudaError_t e = cudaGetLastError();
 	return e == cudaSuccess ? B2NTT_OK : report_cuda_error(e, "b2ntt_general_exec");

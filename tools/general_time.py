@@ -28,7 +28,7 @@ def run(log_h, iters=3):
     ms_g = timed(lambda: g.exec(x), iters)
     ms_f = timed(lambda: plan.exec(x), iters)
     n = 1 << log_h
-    print(json.dumps({"config": "general-basis GF(2^128) additive NTT", "log_h": log_h, "launches": log_h, "ms": round(ms_g, 3),
+    print(json.dumps({"config": "general-basis GF(2^128) additive NTT", "log_h": log_h, "launches": (log_h + 1) // 2 if log_h >= 11 else log_h, "ms": round(ms_g, 3),
                       "elements_per_s": n / ms_g * 1e3, "alg_GBps": round(32 * n / ms_g / 1e6, 1),
                       "fast_path_ms_same_size": round(ms_f, 3)}), flush=True)
     g.close(), plan.close()
