@@ -126,6 +126,8 @@ class Plan:
             raise ValueError(f"{name}: need a contiguous CUDA int32/uint32 tensor")
         if t.numel() != words:
             raise ValueError(f"{name}: expected {words} words, got {t.numel()}")
+        if t.device.index != self.device:
+            raise ValueError(f"{name}: tensor lives on cuda:{t.device.index}, the plan on cuda:{self.device}")
 
     def exec(self, d_in, d_out=None, stream=None):
         """Forward transform of device tensors (32-bit words).  Returns d_out."""

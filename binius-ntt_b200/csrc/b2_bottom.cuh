@@ -34,7 +34,7 @@ struct BottomSmem {
 // One CTA runs kBottomTeams teams of 4 warps, each on its own tile.  Warps w and w + 4 share an SM sub-partition and
 // meet at the same CTA barriers, so they execute the same stretch of straight-line butterfly code at the same time:
 // the instruction cache serves both (two independent CTAs per SM ran out of phase and stalled on instruction fetch).
-// layout: [consts 1024][TL 512][IL 5*512][LT 160]  then per team  [leaves 15*81*4][tw 16][TH 8][IH 8][slots 16*32*36]
+// layout: [consts 1024][TL 512][IL 5*512][LT 160]  then per team  [coefficient rows 15*108*4][tw 16][TH 8][IH 8][slots 16*32*36]
 constexpr int kBottomTeams = 2;
 B2_HD size_t bottom_team_words() { return (size_t)kUpperMaxTw * kLeafPitch + 16 + 8 + 8 + (size_t)16 * 32 * kUSlotWords; }
 B2_HD size_t bottom_smem_words() { return 1024 + 512 + 5 * 512 + 160 + kBottomTeams * bottom_team_words(); }
@@ -45,7 +45,7 @@ B2_HD BottomSmem bottom_smem_view(uint32_t* base, int team = 0) {
 	b.IL = b.TL + 512;
 	b.LT = b.IL + 5 * 512;
 	uint32_t* t = b.LT + 160 + (size_t)team * bottom_team_words();
-	b.us.leaves = reinterpret_cast<Mask4*>(t);
+	b.us.leaves = reinterpret_cast<Coef4*>(t);
 	b.us.tw = t + kUpperMaxTw * kLeafPitch;
 	b.TH = b.us.tw + 16;
 	b.IH = b.TH + 8;

@@ -204,7 +204,7 @@ extern "C" int b2ntt_general_create(b2ntt_general** out, int log_h, const uint32
 	b2ntt_general* g = new (std::nothrow) b2ntt_general;
 	if (!g) return B2NTT_ENOMEM;
 	g->log_h = log_h, g->device = device, g->C.swap(C);
-	cudaSetDevice(device);
+	DeviceGuard guard(device);
 	cudaDeviceGetAttribute(&g->sms, cudaDevAttrMultiProcessorCount, device);
 	cudaFuncSetAttribute(general_layer_cta_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGeneralSmemBytes);
 	cudaFuncSetAttribute(general_layer_cta_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGeneralSmemBytes);
@@ -225,7 +225,7 @@ extern "C" int b2ntt_general_create(b2ntt_general** out, int log_h, const uint32
 
 extern "C" int b2ntt_general_destroy(b2ntt_general* g) {
 	if (!g) return B2NTT_OK;
-	cudaSetDevice(g->device);
+	DeviceGuard guard(g->device);
 	cudaFree(g->d_C);
 	delete g;
 	return B2NTT_OK;
@@ -241,7 +241,8 @@ extern "C" int b2ntt_general_constants(const b2ntt_general* g, uint32_t* h_out) 
 extern "C" int b2ntt_general_exec(b2ntt_general* g, const void* d_in, void* d_out, int inverse, void* stream) {
 	if (!g || !d_in || !d_out) return B2NTT_EINVAL;
 	cudaStream_t st = (cudaStream_t)stream;
-	cudaSetDevice(g->device);
+	if (pointer_device(d_in) != g->device || pointer_device(d_out) != g->device) return B2NTT_EINVAL;
+	DeviceGuard guard(g->device);
 	const uint64_t n = uint64_t(1) << g->log_h, n_half = n >> 1;
 	if (d_in != d_out) {
 		cudaError_t e = cudaMemcpyAsync(d_out, d_in, n * sizeof(gf128), cudaMemcpyDeviceToDevice, st);

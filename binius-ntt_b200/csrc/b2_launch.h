@@ -34,6 +34,31 @@ int launch_bitslice(uint32_t* d, uint64_t n_blocks, int width_bits, int dir, cud
 int launch_mul(int field_bits, int layout, const uint32_t* a, const uint32_t* b, uint32_t* out, uint64_t n, cudaStream_t stream);
 int launch_mul_repeat(int field_bits, uint32_t* io, uint64_t n_threads, int iters, cudaStream_t stream);
 
+// Every ABI call runs on its object's device and leaves the caller's current device as it found it
+// (the reference uses "the current device" implicitly, utils/common.cu:18-20; a plan here is bound to one).
+struct DeviceGuard {
+	int prev = -1, want;
+	cudaError_t err = cudaSuccess;
+	explicit DeviceGuard(int device) : want(device) {
+		err = cudaGetDevice(&prev);
+		if (err == cudaSuccess && prev != want) err = cudaSetDevice(want);
+	}
+	~DeviceGuard() {
+		if (prev >= 0 && prev != want) cudaSetDevice(prev);
+	}
+	DeviceGuard(const DeviceGuard&) = delete;
+	DeviceGuard& operator=(const DeviceGuard&) = delete;
+};
+// device that owns a device pointer, -1 for host / unknown memory (cudaPointerGetAttributes)
+inline int pointer_device(const void* p) {
+	cudaPointerAttributes a;
+	if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+		cudaGetLastError();
+		return -1;
+	}
+	return (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged) ? a.device : -1;
+}
+
 // records the CUDA error text for b2ntt_last_cuda_error() and returns B2NTT_ECUDA (b2ntt.cu)
 int report_cuda_error(cudaError_t e, const char* where);
 

@@ -98,7 +98,8 @@ int launch_bitslice(uint32_t* d, uint64_t n_blocks, int width_bits, int dir, cud
 // element-wise products
 // ------------------------------------------------------------------------------------------------
 template <int H>
-__global__ void mul_compact_kernel(const uint32_t* __restrict__ a, const uint32_t* __restrict__ b, uint32_t* __restrict__ o, uint64_t n) {
+// the output may alias either input (include/b2ntt.h), so none of the multiply kernels declares __restrict__
+__global__ void mul_compact_kernel(const uint32_t* a, const uint32_t* b, uint32_t* o, uint64_t n) {
 	for (uint64_t g = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; g < n; g += (uint64_t)gridDim.x * blockDim.x)
 		o[g] = (uint32_t)Tower<H>::mul(a[g], b[g]);
 }
@@ -106,7 +107,7 @@ __global__ void mul_compact_kernel(const uint32_t* __restrict__ a, const uint32_
 // compact GF(2^32) (multiply<5>, finite_fields/binary_tower.cuh): a warp stages 32 lines per operand through shared
 // memory (coalesced), each lane bit-slices its own line of 32 elements in registers, multiplies bit-sliced and
 // transposes the products back -- ~1.5k logic instructions per 32 products instead of one tower recursion per element.
-__global__ void __launch_bounds__(128) mul_compact32_kernel(const uint32_t* __restrict__ a, const uint32_t* __restrict__ b, uint32_t* __restrict__ o, uint64_t n) {
+__global__ void __launch_bounds__(128) mul_compact32_kernel(const uint32_t* a, const uint32_t* b, uint32_t* o, uint64_t n) {
 	__shared__ uint32_t sm[4][32 * 33];
 	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 	uint32_t* s = sm[warp];
@@ -148,7 +149,7 @@ __global__ void __launch_bounds__(128) mul_compact32_kernel(const uint32_t* __re
 }
 
 // bit-sliced GF(2^32): one thread per block of 32 products, everything in registers
-__global__ void __launch_bounds__(128) mul_sliced32_kernel(const uint32_t* __restrict__ a, const uint32_t* __restrict__ b, uint32_t* __restrict__ o, uint64_t n_blocks) {
+__global__ void __launch_bounds__(128) mul_sliced32_kernel(const uint32_t* a, const uint32_t* b, uint32_t* o, uint64_t n_blocks) {
 	for (uint64_t g = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; g < n_blocks; g += (uint64_t)gridDim.x * blockDim.x) {
 		uint32_t x[32], y[32], z[32];
 		const uint4* pa = reinterpret_cast<const uint4*>(a + g * 32);
@@ -176,7 +177,7 @@ __global__ void __launch_bounds__(128) mul_sliced32_kernel(const uint32_t* __res
 // the product runs bit-sliced as above and warps 0..3 transpose the result rows back before the store.  n_chunks = number
 // of valid 16-byte chunks (= elements when compact), so a ragged last block is neither read nor written past its end.
 template <bool COMPACT>
-__global__ void __launch_bounds__(kMulThreads, B2_MUL128_CTAS) mul_sliced128_kernel(const uint32_t* __restrict__ a, const uint32_t* __restrict__ b, uint32_t* __restrict__ o, uint64_t n_blocks, uint64_t n_chunks) {
+__global__ void __launch_bounds__(kMulThreads, B2_MUL128_CTAS) mul_sliced128_kernel(const uint32_t* a, const uint32_t* b, uint32_t* o, uint64_t n_blocks, uint64_t n_chunks) {
 	extern __shared__ __align__(16) uint32_t msm[];
 	const MulSmem m = mul_smem_view(msm);
 	uint32_t *sa = m.sa, *sb = m.sb;

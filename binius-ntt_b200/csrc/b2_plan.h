@@ -126,7 +126,7 @@ inline int plan_build(HostPlan& hp, int field_bits, int layout, int log_h, int l
 			hp.passes.push_back(PassDesc{q, kt, 0, 0});
 		}
 		// from the top: 6 line bits per pass while none of their stages has a full GF(2^32) twiddle (class 5 needs the
-		// 81-group leaf table, which only fits for 15 twiddles), then 4, with one pass of 2 when the count asks for it
+		// 108-row coefficient table, which only fits for 15 twiddles), then 4, with one pass of 2 when the count asks for it
 		auto cheap6 = [&](int qtop) {  // stages of the line bits [qtop - 6, qtop)
 			for (int bq = qtop - 6; bq < qtop; bq++)
 				if (hp.cls[hp.n_inline + bq - hp.batch_bits] == 5) return false;
@@ -241,10 +241,10 @@ inline void plan_fill_upper(const HostPlan& hp, UpperParams& U, int n, const uin
 	U.dst_sliced = (hp.sliced_io || !last_pass) ? 1 : 0;
 	U.inverse = inverse ? 1 : 0;
 	U.n_groups = (uint64_t)rows << (hp.nb - pd.k - U.ls);
-	U.lpitch = 27;
+	U.lpitch = kLeafRows4;
 	for (int i = 0; i < pd.k; i++) {
 		U.cls[i] = hp.cls[U.stage0 + i];
-		if (U.cls[i] == 5) U.lpitch = 81;
+		if (U.cls[i] == 5) U.lpitch = kLeafRows5;
 	}
 }
 
@@ -254,7 +254,7 @@ inline void plan_fill_bottom(const HostPlan& hp, BottomParams& B, int n, const u
 	memset(&B, 0, sizeof B);
 	plan_fill_upper(hp, B.up, n, src, dst, consts, inverse, coset, one_coset);
 	UpperParams& U = B.up;
-	U.q0 = 5, U.k = 4, U.ls = 5, U.lpitch = 81;
+	U.q0 = 5, U.k = 4, U.ls = 5, U.lpitch = kLeafRows5;
 	U.stage0 = hp.n_inline + 5 - hp.batch_bits;
 	const bool single = inverse || one_coset;
 	const int rows = single ? hp.batch : hp.batch << hp.log_rate;

@@ -191,7 +191,7 @@ extern "C" int b2ntt_sumcheck_create(b2ntt_sumcheck** out, int num_vars, int com
 	b2ntt_sumcheck* s = new (std::nothrow) b2ntt_sumcheck;
 	if (!s) return B2NTT_ENOMEM;
 	s->num_vars = num_vars, s->C = composition_size, s->device = device, s->n0 = uint64_t(1) << num_vars;
-	cudaSetDevice(device);
+	DeviceGuard guard(device);
 	cudaDeviceGetAttribute(&s->sms, cudaDevAttrMultiProcessorCount, device);
 	if (cudaMalloc(&s->d_out, (kScMaxC + 1) * 128 * sizeof(uint32_t)) != cudaSuccess || cudaMalloc(&s->d_coeff, 128 * sizeof(uint32_t)) != cudaSuccess) {
 		cudaFree(s->d_out);
@@ -207,7 +207,7 @@ extern "C" int b2ntt_sumcheck_create(b2ntt_sumcheck** out, int num_vars, int com
 
 extern "C" int b2ntt_sumcheck_destroy(b2ntt_sumcheck* s) {
 	if (!s) return B2NTT_OK;
-	cudaSetDevice(s->device);
+	DeviceGuard guard(s->device);
 	if (s->owns_evals) cudaFree(s->d_evals);
 	cudaFree(s->d_out), cudaFree(s->d_coeff);
 	delete s;
@@ -230,7 +230,8 @@ static int sc_adopt(b2ntt_sumcheck* s, int transposed) {
 
 extern "C" int b2ntt_sumcheck_load_host(b2ntt_sumcheck* s, const void* h_evals, int transposed) {
 	if (!s || !h_evals) return B2NTT_EINVAL;
-	SCU(cudaSetDevice(s->device));
+	DeviceGuard guard(s->device);
+	SCU(guard.err);
 	const size_t bytes = (size_t)s->C * s->n0 * 16;
 	if (!s->owns_evals) {
 		s->d_evals = nullptr;
@@ -243,7 +244,9 @@ extern "C" int b2ntt_sumcheck_load_host(b2ntt_sumcheck* s, const void* h_evals, 
 
 extern "C" int b2ntt_sumcheck_load_device(b2ntt_sumcheck* s, void* d_evals, int transposed) {
 	if (!s || !d_evals) return B2NTT_EINVAL;
-	SCU(cudaSetDevice(s->device));
+	if (pointer_device(d_evals) != s->device) return B2NTT_EINVAL;
+	DeviceGuard guard(s->device);
+	SCU(guard.err);
 	if (s->owns_evals) cudaFree(s->d_evals);
 	s->owns_evals = false, s->d_evals = (uint32_t*)d_evals;
 	return sc_adopt(s, transposed);
@@ -279,7 +282,8 @@ extern "C" int b2ntt_sumcheck_round_messages(b2ntt_sumcheck* s, uint32_t* sum, u
 		memcpy(s->last_points, points, (C + 1) * 16), s->points_round = s->round;
 		return B2NTT_OK;
 	}
-	SCU(cudaSetDevice(s->device));
+	DeviceGuard guard(s->device);
+	SCU(guard.err);
 	const uint64_t half_rows = n / 64;
 	SCU(cudaMemsetAsync(s->d_out, 0, (C + 1) * 128 * sizeof(uint32_t), nullptr));
 	uint64_t ctas = (half_rows + 31) / 32;
@@ -326,7 +330,8 @@ extern "C" int b2ntt_sumcheck_next_round(b2ntt_sumcheck* s, const uint32_t* chal
 		s->round++;
 		return B2NTT_OK;
 	}
-	SCU(cudaSetDevice(s->device));
+	DeviceGuard guard(s->device);
+	SCU(guard.err);
 	// repeat_value_bitsliced (utils/bitslicing.cuh:66-78): word 32k + b = all-ones iff bit b of limb k of the challenge
 	uint32_t coeff[128];
 	for (int k = 0; k < 4; k++)

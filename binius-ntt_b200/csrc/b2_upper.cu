@@ -111,7 +111,7 @@ static int launch_upper_t(const UpperParams& P, cudaStream_t stream) {
 
 int launch_upper(const UpperParams& P, cudaStream_t stream) {
 	if (P.k != 2 && P.k != 4 && P.k != 6) return -1;
-	if (P.ls != (P.k == 6 ? 3 : 5) || (P.lpitch != 81 && P.lpitch != 27) || (P.k == 6 && P.lpitch != 27)) return -1;
+	if (P.ls != (P.k == 6 ? 3 : 5) || (P.lpitch != kLeafRows5 && P.lpitch != kLeafRows4) || (P.k == 6 && P.lpitch != kLeafRows4)) return -1;
 	return P.inverse ? launch_upper_t<true>(P, stream) : launch_upper_t<false>(P, stream);
 }
 

@@ -19,14 +19,17 @@
 // Replaces, for these layers, additive_ntt_kernel (ntt/additive_ntt.cuh:91-160).  The phase
 // functions take the thread identity as arguments so tests/emul can drive them on the CPU.
 #pragma once
+#include "b2_constmat.cuh"
 #include "b2_pass.cuh"
 
 namespace b2 {
 
 constexpr int kUpperWarps = 4;        // warps per CTA
-constexpr int kLeafPitch = 81 * 4;    // words per twiddle in the leaf-mask table (class 5: 81 GF(4) groups x {m0, m1, m0^m1, pad})
+constexpr int kLeafRows5 = 108;       // coefficient rows (Coef4) per twiddle of class 5: 27 GF(16) leaves x 4 output bits (b2_constmat.cuh)
+constexpr int kLeafRows4 = 36;        // ... when no layer of the pass is above class 4: 9 leaves
+constexpr int kLeafPitch = kLeafRows5 * 4;  // words per twiddle in the coefficient table
 constexpr int kUpperMaxTw = 15;       // twiddles of a k = 4 group: 8 + 4 + 2 + 1
-constexpr int kLeafTableWords = 63 * 27 * 4;  // the larger of 15 x 81 (k = 4, class 5) and 63 x 27 (k = 6, classes <= 4) leaf groups
+constexpr int kLeafTableWords = 63 * kLeafRows4 * 4;  // the larger of 15 x 108 (k = 4, class 5) and 63 x 36 (k = 6, classes <= 4) rows
 
 struct alignas(16) Mask4 {
 	uint32_t x, y, z, w;
@@ -131,7 +134,7 @@ struct UpperParams {
 	int nb;                // line bits per row
 	int q0, k;             // this pass owns line bits [q0, q0+k), q0 >= 5, k = 2, 4 or 6
 	int ls;                // log2 of the lines per super-line: 5 (k = 2, 4), 3 (k = 6)
-	int lpitch;            // leaf groups per twiddle in the table: 81, or 27 when no layer of the pass has class 5
+	int lpitch;            // coefficient rows per twiddle in the table: 108, or 36 when no layer of the pass has class 5
 	int stage0;            // butterfly stage of local bit 0
 	int src_sliced, dst_sliced;  // lines are bundles already / stay bundles (no 32x32 transpose)
 	int inverse;
@@ -145,14 +148,14 @@ B2_HD size_t upper_smem_words(int k) {
 	return (size_t)kLeafTableWords + 64 + 1024 + (size_t)512 * kUSlotWords;
 }
 struct UpperSmem {
-	Mask4* leaves;     // [2^k - 1][lpitch]
+	Coef4* leaves;     // [2^k - 1][lpitch] coefficient rows (b2_constmat.cuh)
 	uint32_t* tw;      // [64] twiddle words
 	uint32_t* consts;  // [32][32] copy of the subspace constants
 	uint32_t* slots;   // [512 lines][kUSlotWords]: super-line x, line l at (x << ls) + l; k = 2: 4 super-lines per warp
 };
 B2_HD UpperSmem upper_smem_view(uint32_t* base) {
 	UpperSmem sm;
-	sm.leaves = reinterpret_cast<Mask4*>(base);
+	sm.leaves = reinterpret_cast<Coef4*>(base);
 	sm.tw = base + kLeafTableWords;
 	sm.consts = sm.tw + 64;
 	sm.slots = sm.consts + 1024;
@@ -192,16 +195,16 @@ B2_HD void upper_twiddles(const UpperParams& P, UpperSmem& sm, const UGroup& c, 
 		if ((ind >> b) & 1) w ^= t[b];
 	sm.tw[tid] = w;
 }
-// leaf masks of every twiddle: item = twiddle * lpitch + group, strided over nthreads
+// coefficient rows of every twiddle: item = twiddle * lpitch + leaf * 4 + output bit, strided over nthreads
 B2_HD void upper_leaves(const UpperParams& P, UpperSmem& sm, int tid, int nthreads) {
 	const int ntw = (1 << P.k) - 1, lp = P.lpitch;
 	for (int item = tid; item < ntw * lp; item += nthreads) {
-		const int tw = lp == 81 ? (item * 1619) >> 17 : (item * 607) >> 14;  // item / 81 (item < 1300), item / 27 (item < 1800)
-		const int g = item - tw * lp;
+		const int tw = lp == kLeafRows5 ? (item * 607) >> 16 : (item * 1821) >> 16;  // item / 108 (item < 1620), item / 36 (item < 2268)
+		const int r = item - tw * lp;
 		int lg = 0;
 		while ((tw + 1) >> (lg + 1)) lg++;
 		const int hw = P.cls[P.k - 1 - lg];
-		if (g < leaf_groups(hw)) sm.leaves[tw * lp + g] = leaf_group(sm.tw[tw], hw, g);
+		if ((r >> 2) < coef_leaves(hw)) sm.leaves[tw * lp + r] = coef_row(coef_leaf_value(sm.tw[tw], hw, r >> 2), r & 3);
 	}
 }
 
@@ -253,7 +256,7 @@ B2_HD void upper_pair(const UpperParams& P, const UpperSmem& sm, int lane, int x
 				transpose32(U);
 				transpose32(V);
 			}
-			butterfly_const_dispatch<INV>(cls, U, V, sm.leaves + P.lpitch * upper_tw_index(k, bit, xu));
+			butterfly_mat_dispatch<INV>(cls, U, V, sm.leaves + P.lpitch * upper_tw_index(k, bit, xu));
 			if (last && step == 1 && !P.dst_sliced) {
 				transpose32(U);
 				transpose32(V);

@@ -76,7 +76,8 @@ extern "C" int b2ntt_plan_create(b2ntt_plan** out, int field_bits, int layout, i
 		return B2NTT_EINVAL;
 	}
 	p->device = device;
-	cudaError_t e = cudaSetDevice(device);
+	DeviceGuard guard(device);
+	cudaError_t e = guard.err;
 	if (e == cudaSuccess) e = cudaMalloc(&p->d_consts, sizeof p->hp.consts);
 	if (e == cudaSuccess) e = cudaMalloc(&p->d_lane_tw, sizeof p->hp.lane_tw);
 	if (e == cudaSuccess) e = cudaMemcpy(p->d_consts, p->hp.consts, sizeof p->hp.consts, cudaMemcpyHostToDevice);
@@ -92,7 +93,7 @@ extern "C" int b2ntt_plan_create(b2ntt_plan** out, int field_bits, int layout, i
 
 extern "C" int b2ntt_plan_destroy(b2ntt_plan* p) {
 	if (!p) return B2NTT_OK;
-	cudaSetDevice(p->device);
+	DeviceGuard guard(p->device);
 	if (p->d_consts) cudaFree(p->d_consts);
 	if (p->d_lane_tw) cudaFree(p->d_lane_tw);
 	if (p->d_in) cudaFree(p->d_in);
@@ -117,7 +118,10 @@ static int run(b2ntt_plan* p, const void* d_in, void* d_out, bool inverse, int c
 	if (!d_in || !d_out) return B2NTT_EINVAL;
 	const bool single = inverse || one_coset;
 	if (d_in == d_out && hp.log_rate != 0 && !single) return B2NTT_EINVAL;
-	CU(cudaSetDevice(p->device));
+	// the buffers must live on the plan's device (a pointer of another GPU would be dereferenced by this one's kernels)
+	if (pointer_device(d_in) != p->device || pointer_device(d_out) != p->device) return B2NTT_EINVAL;
+	DeviceGuard guard(p->device);
+	CU(guard.err);
 	const uint32_t* src = (const uint32_t*)d_in;
 	uint32_t* dst = (uint32_t*)d_out;
 	if (hp.tiny) {
@@ -172,7 +176,8 @@ extern "C" int b2ntt_exec_profile(b2ntt_plan* p, const void* d_in, void* d_out, 
 	if (p->hp.tiny) return B2NTT_EUNSUPPORTED;
 	const int np = (int)p->hp.passes.size();
 	if (np > max_passes || np > 15) return B2NTT_EINVAL;
-	CU(cudaSetDevice(p->device));
+	DeviceGuard guard(p->device);
+	CU(guard.err);
 	cudaEvent_t ev[16];
 	for (int i = 0; i <= np; i++) CU(cudaEventCreate(&ev[i]));
 	int rc = run(p, d_in, d_out, false, 0, (cudaStream_t)stream, false, ev);
@@ -201,7 +206,9 @@ extern "C" int b2ntt_exec_top(b2ntt_plan* p, void* d_buf, int log_segments, void
 	if (!p || !d_buf) return B2NTT_EINVAL;
 	PassParams P;
 	if (p->hp.tiny || plan_fill_top(p->hp, P, log_segments, (uint32_t*)d_buf, p->d_consts, p->d_lane_tw)) return B2NTT_EINVAL;
-	CU(cudaSetDevice(p->device));
+	if (pointer_device(d_buf) != p->device) return B2NTT_EINVAL;
+	DeviceGuard guard(p->device);
+	CU(guard.err);
 	if (launch_pass(P, (cudaStream_t)stream)) return cuda_fail(cudaGetLastError(), "launch_pass");
 	return B2NTT_OK;
 }
@@ -210,7 +217,8 @@ extern "C" int b2ntt_exec_host(b2ntt_plan* p, const void* h_in, size_t n_in, voi
 	if (!p || !h_in || !h_out) return B2NTT_EINVAL;
 	const HostPlan& hp = p->hp;
 	if (n_in != ((size_t)1 << hp.log_h)) return B2NTT_EINVAL;  // additive_ntt.cuh:206-208
-	CU(cudaSetDevice(p->device));
+	DeviceGuard guard(p->device);
+	CU(guard.err);
 	if (!p->stream) CU(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
 	const size_t ib = in_words(hp) * 4, ob = out_words(hp) * 4;
 	if (!p->d_out) {
@@ -239,7 +247,8 @@ extern "C" int b2ntt_exec_host_batch(b2ntt_plan* p, const void* const* h_in, siz
 	for (int i = 0; i < count; i++)
 		if (!h_in[i] || !h_out[i]) return B2NTT_EINVAL;
 	if (count == 0) return B2NTT_OK;
-	CU(cudaSetDevice(p->device));
+	DeviceGuard guard(p->device);
+	CU(guard.err);
 	const size_t ib = in_words(hp) * 4, ob = out_words(hp) * 4;
 	constexpr int K = b2ntt_plan::kPipe;
 	if (!p->pipe_ready) {
@@ -294,6 +303,10 @@ extern "C" int b2ntt_bitslice(void* d_buf, size_t n_blocks, int width_bits, int 
 	if (dir != 0 && dir != 1) return B2NTT_EINVAL;
 	if (n_blocks == 0) return B2NTT_OK;
 	if (!d_buf) return B2NTT_EINVAL;
+	const int dev = pointer_device(d_buf);
+	if (dev < 0) return B2NTT_EINVAL;
+	DeviceGuard guard(dev);
+	CU(guard.err);
 	if (launch_bitslice((uint32_t*)d_buf, n_blocks, width_bits, dir, (cudaStream_t)stream)) return cuda_fail(cudaGetLastError(), "bitslice");
 	return B2NTT_OK;
 }
@@ -307,6 +320,10 @@ extern "C" int b2ntt_mul(int field_bits, int layout, const void* a, const void* 
 		return B2NTT_EINVAL;
 	if (n == 0) return B2NTT_OK;
 	if (!a || !b || !o) return B2NTT_EINVAL;
+	const int dev = pointer_device(o);
+	if (dev < 0 || pointer_device(a) != dev || pointer_device(b) != dev) return B2NTT_EINVAL;
+	DeviceGuard guard(dev);
+	CU(guard.err);
 	if (launch_mul(field_bits, layout, (const uint32_t*)a, (const uint32_t*)b, (uint32_t*)o, n, (cudaStream_t)stream))
 		return cuda_fail(cudaGetLastError(), "mul");
 	return B2NTT_OK;
@@ -315,6 +332,10 @@ extern "C" int b2ntt_mul(int field_bits, int layout, const void* a, const void* 
 extern "C" int b2ntt_mul_repeat(int field_bits, void* d_io, size_t n_threads, int iters, void* stream) {
 	if (field_bits != 32) return field_bits == 128 ? B2NTT_EUNSUPPORTED : B2NTT_EINVAL;
 	if (!d_io || iters < 0) return B2NTT_EINVAL;
+	const int dev = pointer_device(d_io);
+	if (dev < 0) return B2NTT_EINVAL;
+	DeviceGuard guard(dev);
+	CU(guard.err);
 	if (launch_mul_repeat(field_bits, (uint32_t*)d_io, n_threads, iters, (cudaStream_t)stream)) return cuda_fail(cudaGetLastError(), "mul_repeat");
 	return B2NTT_OK;
 }

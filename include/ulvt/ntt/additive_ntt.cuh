@@ -18,7 +18,10 @@ class AdditiveNTT {
 public:
 	explicit AdditiveNTT(const AdditiveNTTConf<T, P>& conf) : ntt_conf(conf) {
 		// a GF(2^128) transform still draws its domain from GF(2^32): log_h + log_rate <= 32
-		const int rc = b2ntt_plan_create(&plan, (int)(sizeof(T) * 8), B2NTT_LAYOUT_COMPACT, conf.log_h, conf.log_rate, 1, 0);
+		// the plan lives on the caller's CURRENT device, as the reference's cudaMalloc'd members do (additive_ntt.cuh:184-198)
+		int device = 0;
+		cudaGetDevice(&device);
+		const int rc = b2ntt_plan_create(&plan, (int)(sizeof(T) * 8), B2NTT_LAYOUT_COMPACT, conf.log_h, conf.log_rate, 1, device);
 		if (rc != B2NTT_OK) {
 			std::cerr << "AdditiveNTT: " << b2ntt_strerror(rc) << " " << b2ntt_last_cuda_error() << std::endl;
 			plan = nullptr;
@@ -56,7 +59,8 @@ private:
 class GeneralAdditiveNTT {
 public:
 	GeneralAdditiveNTT(int log_h, const b128* basis) : log_h(log_h) {
-		const int rc = b2ntt_general_create(&g, log_h, reinterpret_cast<const uint32_t*>(basis), 0);
+		cudaGetDevice(&device);
+		const int rc = b2ntt_general_create(&g, log_h, reinterpret_cast<const uint32_t*>(basis), device);
 		if (rc != B2NTT_OK) {
 			std::cerr << "GeneralAdditiveNTT: " << b2ntt_strerror(rc) << " " << b2ntt_last_cuda_error() << std::endl;
 			g = nullptr;
@@ -64,17 +68,29 @@ public:
 	}
 	GeneralAdditiveNTT(const GeneralAdditiveNTT&) = delete;
 	GeneralAdditiveNTT& operator=(const GeneralAdditiveNTT&) = delete;
-	~GeneralAdditiveNTT() { b2ntt_general_destroy(g); }
+	~GeneralAdditiveNTT() {
+		b2ntt_general_destroy(g);
+		if (d_stage) {
+			int cur = 0;
+			cudaGetDevice(&cur);
+			cudaSetDevice(device);
+			cudaFree(d_stage);
+			cudaSetDevice(cur);
+		}
+	}
 	bool valid() const { return g != nullptr; }
 
 	bool apply(const NTTData<b128>& input, NTTData<b128>& output, bool inverse = false) {
 		if (!g || input.size != ((size_t)1 << log_h) || input.order != DataOrder::IN_ORDER) return false;
 		const size_t bytes = input.size * sizeof(b128);
-		void* d = nullptr;
-		if (cudaMalloc(&d, bytes) != cudaSuccess) return false;
-		bool ok = cudaMemcpy(d, input.data.get(), bytes, cudaMemcpyHostToDevice) == cudaSuccess && b2ntt_general_exec(g, d, d, inverse, nullptr) == B2NTT_OK &&
-		          cudaMemcpy(output.data.get(), d, bytes, cudaMemcpyDeviceToHost) == cudaSuccess;
-		cudaFree(d);
+		int cur = 0;
+		cudaGetDevice(&cur);
+		cudaSetDevice(device);  // the staging buffer (kept across calls) lives on the object's device
+		bool ok = d_stage || cudaMalloc(&d_stage, bytes) == cudaSuccess;
+		ok = ok && cudaMemcpy(d_stage, input.data.get(), bytes, cudaMemcpyHostToDevice) == cudaSuccess &&
+		     b2ntt_general_exec(g, d_stage, d_stage, inverse, nullptr) == B2NTT_OK &&
+		     cudaMemcpy(output.data.get(), d_stage, bytes, cudaMemcpyDeviceToHost) == cudaSuccess;
+		cudaSetDevice(cur);
 		if (ok) output.order = DataOrder::IN_ORDER;
 		return ok;
 	}
@@ -84,5 +100,7 @@ public:
 
 private:
 	int log_h;
+	int device = 0;
+	void* d_stage = nullptr;
 	b2ntt_general* g = nullptr;
 };

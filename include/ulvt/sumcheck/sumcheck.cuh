@@ -3,6 +3,8 @@
 // of COMPOSITION_SIZE columns of 2^NUM_VARS GF(2^128) evaluations, compact or bit-sliced; the `benchmarking` flag keeps
 // the three time stamps), same this_round_messages / move_to_next_round.  NUM_VARS 5..30 (the reference: 20, 24, 28).
 #pragma once
+#include <cuda_runtime.h>
+
 #include <array>
 #include <chrono>
 #include <cstdint>
@@ -27,7 +29,9 @@ public:
 	std::chrono::time_point<std::chrono::high_resolution_clock> start_before_memcpy, start_before_transpose, start_raw;
 
 	Sumcheck(const std::vector<uint32_t>& evals_span, const bool benchmarking) {
-		int rc = b2ntt_sumcheck_create(&sc, NUM_VARS, COMPOSITION_SIZE, 0);
+		int device = 0;
+		cudaGetDevice(&device);  // the caller's current device, as the reference's cudaMalloc calls use
+		int rc = b2ntt_sumcheck_create(&sc, NUM_VARS, COMPOSITION_SIZE, device);
 		report(rc, "Sumcheck");
 		if (benchmarking) start_before_memcpy = start_before_transpose = std::chrono::high_resolution_clock::now();
 		// upload and (for compact data) bit-slice in one call; the split of the two stamps is not observable here

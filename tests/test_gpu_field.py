@@ -135,3 +135,54 @@ def test_mul128_field_identities_at_config5_size(b2, cuda):
     s = b2.mul(a, b, 128, b2.api.LAYOUT_BITSLICED)
     b2.bitslice_(s, 128, inverse=True)
     assert torch.equal(s, ab)
+
+
+def test_config5_full_size_vs_oracle(b2, oracle, cuda):
+    """config 5 at its stated size: 2^28 bit-sliced GF(2^128) pairs (2^23 blocks of 32, 4 GiB per operand).  The four
+    reference products of finite_fields/tests/test_fanpaartower.cu:204-273 are planted in the first and the last block;
+    a strided sample of 2^16 blocks is compared with the CPU oracle's bit-sliced multiply."""
+    import torch
+
+    n_blocks, W = 1 << 23, 128
+    g = torch.Generator(device=cuda).manual_seed(528)
+    a = torch.randint(-2**31, 2**31 - 1, (n_blocks * W,), dtype=torch.int32, device=cuda, generator=g)
+    b = torch.randint(-2**31, 2**31 - 1, (n_blocks * W,), dtype=torch.int32, device=cuda, generator=g)
+    case = next(c for c in KATS["bitsliced"] if c["h"] == 7 and len(c["a"]) == 16)
+    ka, kb = np.zeros(W, dtype=np.uint32), np.zeros(W, dtype=np.uint32)
+    ka[:16], kb[:16] = case["a"], case["b"]  # four 128-bit operands, then zero lanes
+    ka_s, kb_s = oracle.bitslice(ka, W), oracle.bitslice(kb, W)
+    for blk in (0, n_blocks - 1):
+        a[blk * W:(blk + 1) * W] = _dev(ka_s, cuda)
+        b[blk * W:(blk + 1) * W] = _dev(kb_s, cuda)
+    out = b2.mul(a, b, 128, b2.api.LAYOUT_BITSLICED)
+    for blk in (0, n_blocks - 1):
+        got = oracle.unbitslice(_host(out[blk * W:(blk + 1) * W]), W)
+        for i, v in case["result"].items():
+            assert got[int(i)] == v, (blk, i)
+        assert not got[16:].any()
+    stride = n_blocks >> 16
+    idx = (torch.arange(1 << 16, device=cuda) * stride + 3).clamp_(max=n_blocks - 1)
+    sa = _host(a.view(n_blocks, W)[idx].reshape(-1))
+    sb = _host(b.view(n_blocks, W)[idx].reshape(-1))
+    so = _host(out.view(n_blocks, W)[idx].reshape(-1))
+    assert np.array_equal(so, oracle.mul_bitsliced(sa, sb, 7))
+
+
+@pytest.mark.parametrize("field_bits,layout", [(32, 0), (32, 1), (128, 0), (128, 1), (8, 0), (16, 0)])
+def test_mul_in_place_aliasing(b2, oracle, cuda, field_bits, layout):
+    """include/b2ntt.h: d_out may alias d_a or d_b (multiply_unrolled's destination may alias an input,
+    sumcheck/core/core.cu:21)"""
+    limbs = max(1, field_bits // 32)
+    n = 32 * 257
+    mask = np.uint32(0xFFFFFFFF if field_bits >= 32 else (1 << field_bits) - 1)
+    a, b = _rand(n * limbs, 71) & mask, _rand(n * limbs, 72) & mask
+    ref = _host(b2.mul(_dev(a, cuda), _dev(b, cuda), field_bits, layout))
+    da, db = _dev(a, cuda), _dev(b, cuda)
+    b2.mul(da, db, field_bits, layout, out=da)
+    assert np.array_equal(_host(da), ref)
+    da = _dev(a, cuda)
+    b2.mul(da, db, field_bits, layout, out=db)
+    assert np.array_equal(_host(db), ref)
+    sq = _host(b2.mul(da, da.clone(), field_bits, layout))
+    b2.mul(da, da, field_bits, layout, out=da)
+    assert np.array_equal(_host(da), sq)

@@ -215,3 +215,70 @@ def test_exec_host_batch_matches_exec_host(b2, oracle, cuda):
         for x, o in zip(xs, outs):
             assert np.array_equal(o, oracle.antt_forward(x, log_h, r, limbs))
         p.close()
+
+
+def test_config2_both_layouts_vs_oracle(b2, oracle, cuda):
+    """config 2 at its stated size (log_n = 24, GF(2^128)): the compact AND the bit-sliced transform against the CPU
+    oracle word for word, plus the reference digest additive_ntt_hashes[0][24] (ntt/tests/test_ntt.cu:79) on limb 0 of
+    both layouts."""
+    import torch
+
+    log_h = 24
+    x = np.empty((1 << log_h, 4), dtype=np.uint32)
+    x[:, 0] = oracle.reference_input(log_h, 0)
+    x[:, 1:] = _rand((1 << log_h) * 3, 24).reshape(-1, 3)
+    ref = oracle.antt_forward(x.reshape(-1), log_h, 0, 4)
+    assert oracle.md5_hex(np.ascontiguousarray(ref.reshape(-1, 4)[:, 0])) == oracle.golden_md5(0, log_h)
+    dx = _dev(x.reshape(-1), cuda)
+    yc = b2.Plan(128, log_h, 0).exec(dx.clone())
+    assert np.array_equal(_host(yc), ref)
+    xs = dx.clone()
+    b2.bitslice_(xs, 128)
+    ys = b2.Plan(128, log_h, 0, layout=b2.api.LAYOUT_BITSLICED).exec(xs)
+    b2.bitslice_(ys, 128, inverse=True)
+    assert torch.equal(ys, yc)
+    assert oracle.md5_hex(_host(ys.view(-1, 4)[:, 0].contiguous())) == oracle.golden_md5(0, log_h)
+
+
+@pytest.mark.parametrize("log_h", [25, 26])
+def test_tile_schedule_bitsliced_limb0_digest(b2, oracle, cuda, log_h):
+    """the upper + tile schedule on bit-sliced images above log_h = 24: limb 0 carries the reference stream"""
+    import torch
+
+    n = 1 << log_h
+    x = torch.randint(-2**31, 2**31 - 1, (n * 4,), dtype=torch.int32, device=cuda, generator=torch.Generator(device=cuda).manual_seed(log_h))
+    x.view(-1, 4)[:, 0] = _dev(oracle.reference_input(log_h, 0), cuda)
+    b2.bitslice_(x, 128)
+    y = b2.Plan(128, log_h, 0, layout=b2.api.LAYOUT_BITSLICED).exec(x)
+    b2.bitslice_(y, 128, inverse=True)
+    assert oracle.md5_hex(_host(y.view(-1, 4)[:, 0].contiguous())) == oracle.golden_md5(0, log_h)
+
+
+def test_wrong_device_pointers_are_rejected(b2, cuda):
+    """a plan is bound to one device: host pointers and tensors of another GPU are refused, and no ABI call changes the
+    caller's current device"""
+    import ctypes as C
+
+    import torch
+
+    plan = b2.Plan(32, 12, 0)
+    host = np.zeros(1 << 12, dtype=np.uint32)
+    rc = b2.lib().b2ntt_exec(plan._h, host.ctypes.data, host.ctypes.data, C.c_void_p(0))
+    assert rc == -1  # B2NTT_EINVAL: not device memory
+    if torch.cuda.device_count() >= 2:
+        other = torch.zeros(1 << 12, dtype=torch.int32, device="cuda:1")
+        with pytest.raises(ValueError):
+            plan.exec(other)
+        assert b2.lib().b2ntt_exec(plan._h, other.data_ptr(), other.data_ptr(), C.c_void_p(0)) == -1
+        # a plan on device 1 used while device 0 is current: right answer, current device untouched
+        p1 = b2.Plan(32, 12, 0, device=1)
+        x = torch.randint(-2**31, 2**31 - 1, (1 << 12,), dtype=torch.int32, device="cuda:1")
+        torch.cuda.set_device(0)
+        with torch.cuda.device(1):
+            s1 = torch.cuda.current_stream().cuda_stream
+        y1 = p1.exec(x.clone(), stream=s1)
+        torch.cuda.synchronize(1)
+        assert torch.cuda.current_device() == 0
+        assert torch.equal(y1.cpu(), plan.exec(x.to("cuda:0")).cpu())
+        p1.close()
+    plan.close()
