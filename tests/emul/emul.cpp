@@ -60,6 +60,29 @@ static void run_upper(const UpperParams& P) {
 	}
 }
 
+// upper passes with warp-owned groups (b2_wupper.cu): one warp walks a 128-line group from copy-in to copy-out
+template <bool INV>
+static void run_wupper(const UpperParams& P) {
+	std::vector<uint32_t> mem(upper_smem_words(4) + 8);
+	UpperSmem sm = upper_smem_view(mem.data());
+	const int T = 256, k = P.k, ls = P.ls, nph = k >> 1;
+	for (uint64_t grp = 0; grp < P.n_groups; grp++) {
+		const UGroup c = upper_group(P, grp);
+		for (int t = 0; t < T; t++) upper_twiddles(P, sm, c, t, P.consts);
+		for (int t = 0; t < T; t++) upper_leaves(P, sm, t, T);
+		for (int lane = 0; lane < 32; lane++) wupper_copy<false>(P, sm.slots, c, lane);
+		for (int e = 0; e < nph; e++) {
+			const int j = INV ? nph - 1 - e : e, b1 = k - 1 - 2 * j, b0 = b1 - 1;
+			for (int lane = 0; lane < 32; lane++) {
+				const int u = lane >> ls;
+				const int xbase = ((u >> b0) << (b1 + 1)) | (u & ((1 << b0) - 1));
+				upper_pair<INV>(P, sm, lane, xbase, b0, 0, b1, e == 0, e == nph - 1);
+			}
+		}
+		for (int lane = 0; lane < 32; lane++) wupper_copy<true>(P, sm.slots, c, lane);
+	}
+}
+
 // lowest pass on 512-line tiles (b2_bottom.cuh): same phase functions as bottom_kernel
 template <bool INV>
 static void run_bottom(const BottomParams& B) {
@@ -88,10 +111,10 @@ static void run_bottom(const BottomParams& B) {
 	}
 }
 
-extern "C" int emul_antt_cta(int field_bits, int layout, int log_h, int log_rate, int batch, const uint32_t* in,
-                             uint32_t* out, int inverse, int coset, int cta_threads, int group_lines) {
+extern "C" int emul_antt_sched(int field_bits, int layout, int log_h, int log_rate, int batch, const uint32_t* in,
+                               uint32_t* out, int inverse, int coset, int cta_threads, int group_lines, int use_upper) {
 	HostPlan hp;
-	if (plan_build(hp, field_bits, layout, log_h, log_rate, batch, cta_threads, group_lines)) return -1;
+	if (plan_build(hp, field_bits, layout, log_h, log_rate, batch, cta_threads, group_lines, use_upper)) return -1;
 	if (hp.tiny) return -4;
 	PassParams P;
 	UpperParams U;
@@ -109,10 +132,19 @@ extern "C" int emul_antt_cta(int field_bits, int layout, int log_h, int log_rate
 			if (inverse) run_upper<true>(U); else run_upper<false>(U);
 			continue;
 		}
+		if (kind == 3) {
+			plan_fill_upper(hp, U, n, in, out, hp.consts, inverse != 0, coset);
+			if (inverse) run_wupper<true>(U); else run_wupper<false>(U);
+			continue;
+		}
 		plan_fill_pass(hp, P, n, in, out, hp.consts, hp.lane_tw, inverse != 0, coset);
 		if (inverse) run_pass<true>(P); else run_pass<false>(P);
 	}
 	return 0;
+}
+extern "C" int emul_antt_cta(int field_bits, int layout, int log_h, int log_rate, int batch, const uint32_t* in,
+                             uint32_t* out, int inverse, int coset, int cta_threads, int group_lines) {
+	return emul_antt_sched(field_bits, layout, log_h, log_rate, batch, in, out, inverse, coset, cta_threads, group_lines, 2);
 }
 extern "C" int emul_antt(int field_bits, int layout, int log_h, int log_rate, int batch, const uint32_t* in,
                          uint32_t* out, int inverse, int coset) {

@@ -126,6 +126,7 @@ def emul():
     E = C.CDLL(p)
     u32p = np.ctypeslib.ndpointer(dtype=np.uint32, flags="C_CONTIGUOUS")
     E.emul_antt.argtypes = [C.c_int] * 5 + [u32p, u32p, C.c_int, C.c_int]
+    E.emul_antt_sched.argtypes = [C.c_int] * 5 + [u32p, u32p] + [C.c_int] * 5
     E.emul_constants.argtypes = [C.c_int, C.c_int, u32p]
     E.emul_gf32_mul.argtypes = [C.c_uint32, C.c_uint32]
     E.emul_gf32_mul.restype = C.c_uint32
@@ -151,6 +152,23 @@ def test_emulated_kernels_match_oracle(oracle, emul, field_bits, layout, log_h, 
     n = (1 << log_h) * limbs
     back = np.zeros(n, dtype=np.uint32)
     assert emul.emul_antt(field_bits, layout, log_h, log_rate, 1, np.ascontiguousarray(out[:n]), back, 1, 0) == 0
+    assert np.array_equal(back, src)
+
+
+@pytest.mark.parametrize("field_bits,layout,log_h,log_rate", [
+    (32, 0, 16, 0), (128, 0, 14, 0), (128, 0, 16, 1), (32, 0, 18, 0), (128, 1, 16, 0), (32, 0, 20, 0), (128, 0, 18, 1), (32, 0, 22, 0)])
+def test_emulated_warp_owned_upper_passes(oracle, emul, field_bits, layout, log_h, log_rate):
+    """schedule 4: the upper passes as warp-owned 128-line groups (b2_wupper.cu; k = 2, 4 and 6) over the tile pass"""
+    limbs = field_bits // 32
+    x = _rand((1 << log_h) * limbs, 31 * log_h + log_rate)
+    src = oracle.bitslice(x, field_bits) if layout else x
+    out = np.zeros((1 << (log_h + log_rate)) * limbs, dtype=np.uint32)
+    assert emul.emul_antt_sched(field_bits, layout, log_h, log_rate, 1, src, out, 0, 0, 0, 0, 4) == 0
+    got = oracle.unbitslice(out, field_bits) if layout else out
+    assert np.array_equal(got, oracle.antt_forward(x, log_h, log_rate, limbs))
+    n = (1 << log_h) * limbs
+    back = np.zeros(n, dtype=np.uint32)
+    assert emul.emul_antt_sched(field_bits, layout, log_h, log_rate, 1, np.ascontiguousarray(out[:n]), back, 1, 0, 0, 0, 4) == 0
     assert np.array_equal(back, src)
 
 
