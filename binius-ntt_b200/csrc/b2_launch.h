@@ -25,7 +25,6 @@ struct TinyParams {
 
 int launch_pass(const PassParams& P, cudaStream_t stream);
 int launch_upper(const UpperParams& U, cudaStream_t stream);  // b2_upper.cu
-int launch_wupper(const UpperParams& U, cudaStream_t stream);  // b2_wupper.cu
 int launch_bottom(const BottomParams& B, cudaStream_t stream);  // b2_bottom.cu
 int launch_tiny_fanout(const TinyParams& T, cudaStream_t stream);
 int launch_tiny_layers(const TinyParams& T, cudaStream_t stream);

@@ -21,7 +21,7 @@ struct PassDesc {
 	int k;        // line bits fused
 	int in_line;  // run the in-line layers in this pass
 	int kind;     // 0: bundle pass through shared memory (b2_pass.cuh), 1: upper pass with warp-uniform twiddles (b2_upper.cuh),
-	              // 2: lowest pass on 512-line tiles (b2_bottom.cuh), 3: upper pass with warp-owned 128-line groups (b2_wupper.cu)
+	              // 2: lowest pass on 512-line tiles (b2_bottom.cuh)
 };
 
 struct HostPlan {
@@ -115,8 +115,6 @@ inline int plan_build(HostPlan& hp, int field_bits, int layout, int log_h, int l
 	hp.tiny = nbf < 1;
 	const bool use_upper6 = use_upper != 3;  // 3: as 2 but without the 6-bit passes (A/B runs)
 	if (use_upper == 3) use_upper = 2;
-	const int ukind = use_upper == 4 ? 3 : 1;  // 4: as 2 with the warp-owned upper passes
-	if (use_upper == 4) use_upper = 2;
 	if (!hp.tiny && use_upper == 2 && nbf >= 9 - hp.batch_bits) {
 		// lowest pass: 512-line tiles (kind 2) = 9 - batch_bits butterfly line bits; above it upper passes of 4
 		// (or 2) line bits; an odd remainder goes to one bundle pass of 3 (or 1) bits at the top
@@ -136,15 +134,15 @@ inline int plan_build(HostPlan& hp, int field_bits, int layout, int log_h, int l
 		};
 		while (use_upper6 && left >= 6 && (left - 6) % 2 == 0 && cheap6(q)) {
 			q -= 6, left -= 6;
-			hp.passes.push_back(PassDesc{q, 6, 0, ukind});
+			hp.passes.push_back(PassDesc{q, 6, 0, 1});
 		}
 		if (left & 3) {
 			q -= 2, left -= 2;
-			hp.passes.push_back(PassDesc{q, 2, 0, ukind});
+			hp.passes.push_back(PassDesc{q, 2, 0, 1});
 		}
 		while (left > 0) {
 			q -= 4, left -= 4;
-			hp.passes.push_back(PassDesc{q, 4, 0, ukind});
+			hp.passes.push_back(PassDesc{q, 4, 0, 1});
 		}
 		hp.passes.push_back(PassDesc{hp.batch_bits, kb, 1, 2});
 	} else if (!hp.tiny && use_upper && nbf > max_bits && max_bits >= 6) {
@@ -237,7 +235,7 @@ inline void plan_fill_upper(const HostPlan& hp, UpperParams& U, int n, const uin
 	U.coset0 = single ? coset : 0;
 	U.consts = consts;
 	U.log_h = hp.log_h, U.nb = hp.nb, U.q0 = pd.q0, U.k = pd.k;
-	U.ls = pd.kind == 3 ? 7 - pd.k : pd.k == 6 ? 3 : 5;  // warp-owned groups are always 128 lines
+	U.ls = pd.k == 6 ? 3 : 5;
 	U.stage0 = hp.n_inline + pd.q0 - hp.batch_bits;
 	U.src_sliced = (hp.sliced_io || !first_pass) ? 1 : 0;
 	U.dst_sliced = (hp.sliced_io || !last_pass) ? 1 : 0;

@@ -295,47 +295,4 @@ B2_HD void upper_copy(const UpperParams& P, const UpperSmem& sm, const UGroup& c
 	}
 }
 
-// ---- warp-owned groups (b2_wupper.cu): 2^k super-lines of 2^(7-k) lines = 128 lines per warp ------------------------
-constexpr int kWGroupLines = 128;  // lines a warp holds at a time: 4 per lane (one radix-4 unit)
-
-// the warp's group between global memory and its slots (slot = line of the group = x << ls | l), 16-byte chunks:
-// lane = (line of four) << 3 | piece, so a warp instruction moves four consecutive slots = 4 (ls >= 2) or 2 + 2 (ls = 1)
-// lines that are contiguous in global memory
-template <bool STORE>
-B2_HD void wupper_copy(const UpperParams& P, uint32_t* slots, const UGroup& c, int lane) {
-	const int ls = P.ls, piece = lane & 7, l4 = lane >> 3;
-	const uint32_t* srow = P.src + (uint64_t)(c.row >> P.src_row_shift) * P.src_row_words;
-	uint32_t* drow = P.dst + (uint64_t)c.row * P.dst_row_words;
-	const uint64_t xstride = (uint64_t)32 << P.q0;  // words between super-lines x and x + 1
-	if (ls >= 2) {
-		const int steps = 1 << (ls - 2), nx = 1 << P.k;
-		uint64_t g = upper_line(P, c, 0, l4) * 32 + piece * 4;
-		uint32_t* s = slots + (size_t)l4 * kUSlotWords + piece * 4;
-#pragma unroll 1
-		for (int x = 0; x < nx; x++) {
-#pragma unroll 2
-			for (int st = 0; st < steps; st++) {
-				if (STORE)
-					copy16_s2g(drow + g + (size_t)st * 128, s + (size_t)st * 4 * kUSlotWords);
-				else
-					copy16_g2s(s + (size_t)st * 4 * kUSlotWords, srow + g + (size_t)st * 128);
-			}
-			g += xstride, s += (size_t)kUSlotWords << ls;
-		}
-	} else {
-		// two lines per super-line: a warp instruction covers the super-lines 2 it and 2 it + 1
-		const int l = l4 & 1, xo = l4 >> 1;
-		uint64_t g = upper_line(P, c, xo, l) * 32 + piece * 4;
-		uint32_t* s = slots + (size_t)l4 * kUSlotWords + piece * 4;
-#pragma unroll 4
-		for (int it = 0; it < kWGroupLines / 4; it++) {
-			if (STORE)
-				copy16_s2g(drow + g, s);
-			else
-				copy16_g2s(s, srow + g);
-			g += 2 * xstride, s += 4 * kUSlotWords;
-		}
-	}
-}
-
 }  // namespace b2

@@ -70,7 +70,7 @@ extern "C" int b2ntt_plan_create(b2ntt_plan** out, int field_bits, int layout, i
 	const int line_bits = log_h + log_rate + (field_bits == 128 ? 2 : 0) - 5;
 	const uint64_t total_lines = (uint64_t)(batch > 0 ? batch : 1) << (line_bits > 0 ? line_bits : 0);
 	int upper = total_lines >= (uint64_t(1) << 22) ? 2 : 0;
-	if (const char* e = getenv("B2NTT_UPPER")) upper = atoi(e);  // tuning knob: 0 = bundle passes only, 1 = upper passes over a bundle pass, 2 = upper passes over the tile pass, 4 = as 2 with warp-owned upper passes
+	if (const char* e = getenv("B2NTT_UPPER")) upper = atoi(e);  // tuning knob: 0 = bundle passes only, 1 = upper passes over a bundle pass, 2 = upper passes over the tile pass
 	if (plan_build(p->hp, field_bits, layout, log_h, log_rate, batch, cta, glines, upper)) {
 		delete p;
 		return B2NTT_EINVAL;
@@ -151,9 +151,9 @@ static int run(b2ntt_plan* p, const void* d_in, void* d_out, bool inverse, int c
 	if (ev) CU(cudaEventRecord(ev[0], st));
 	for (int n = 0; n < np; n++) {
 		const int kind = (inverse ? hp.passes[np - 1 - n] : hp.passes[n]).kind;
-		if (kind == 1 || kind == 3) {
+		if (kind == 1) {
 			plan_fill_upper(hp, U, n, src, dst, p->d_consts, inverse, coset, one_coset);
-			if (kind == 3 ? launch_wupper(U, st) : launch_upper(U, st)) return cuda_fail(cudaGetLastError(), "launch_upper");
+			if (launch_upper(U, st)) return cuda_fail(cudaGetLastError(), "launch_upper");
 		} else if (kind == 2) {
 			plan_fill_bottom(hp, B, n, src, dst, p->d_consts, p->d_lane_tw, inverse, coset, one_coset);
 			if (launch_bottom(B, st)) return cuda_fail(cudaGetLastError(), "launch_bottom");
@@ -184,7 +184,7 @@ extern "C" int b2ntt_exec_profile(b2ntt_plan* p, const void* d_in, void* d_out, 
 	if (rc == B2NTT_OK && cudaEventSynchronize(ev[np]) != cudaSuccess) rc = cuda_fail(cudaGetLastError(), "cudaEventSynchronize");
 	for (int i = 0; i < np && rc == B2NTT_OK; i++) {
 		if (cudaEventElapsedTime(&pass_ms[i], ev[i], ev[i + 1]) != cudaSuccess) rc = cuda_fail(cudaGetLastError(), "cudaEventElapsedTime");
-		if (pass_kind) pass_kind[i] = p->hp.passes[i].kind;  // 0 pass_kernel, 1 upper_kernel, 2 bottom_kernel, 3 wupper_kernel
+		if (pass_kind) pass_kind[i] = p->hp.passes[i].kind;
 	}
 	for (int i = 0; i <= np; i++) cudaEventDestroy(ev[i]);
 	return rc == B2NTT_OK ? np : rc;

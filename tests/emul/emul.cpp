@@ -60,29 +60,6 @@ static void run_upper(const UpperParams& P) {
 	}
 }
 
-// upper passes with warp-owned groups (b2_wupper.cu): one warp walks a 128-line group from copy-in to copy-out
-template <bool INV>
-static void run_wupper(const UpperParams& P) {
-	std::vector<uint32_t> mem(upper_smem_words(4) + 8);
-	UpperSmem sm = upper_smem_view(mem.data());
-	const int T = 256, k = P.k, ls = P.ls, nph = k >> 1;
-	for (uint64_t grp = 0; grp < P.n_groups; grp++) {
-		const UGroup c = upper_group(P, grp);
-		for (int t = 0; t < T; t++) upper_twiddles(P, sm, c, t, P.consts);
-		for (int t = 0; t < T; t++) upper_leaves(P, sm, t, T);
-		for (int lane = 0; lane < 32; lane++) wupper_copy<false>(P, sm.slots, c, lane);
-		for (int e = 0; e < nph; e++) {
-			const int j = INV ? nph - 1 - e : e, b1 = k - 1 - 2 * j, b0 = b1 - 1;
-			for (int lane = 0; lane < 32; lane++) {
-				const int u = lane >> ls;
-				const int xbase = ((u >> b0) << (b1 + 1)) | (u & ((1 << b0) - 1));
-				upper_pair<INV>(P, sm, lane, xbase, b0, 0, b1, e == 0, e == nph - 1);
-			}
-		}
-		for (int lane = 0; lane < 32; lane++) wupper_copy<true>(P, sm.slots, c, lane);
-	}
-}
-
 // lowest pass on 512-line tiles (b2_bottom.cuh): same phase functions as bottom_kernel
 template <bool INV>
 static void run_bottom(const BottomParams& B) {
@@ -130,11 +107,6 @@ extern "C" int emul_antt_sched(int field_bits, int layout, int log_h, int log_ra
 		if (kind == 1) {
 			plan_fill_upper(hp, U, n, in, out, hp.consts, inverse != 0, coset);
 			if (inverse) run_upper<true>(U); else run_upper<false>(U);
-			continue;
-		}
-		if (kind == 3) {
-			plan_fill_upper(hp, U, n, in, out, hp.consts, inverse != 0, coset);
-			if (inverse) run_wupper<true>(U); else run_wupper<false>(U);
 			continue;
 		}
 		plan_fill_pass(hp, P, n, in, out, hp.consts, hp.lane_tw, inverse != 0, coset);

@@ -155,23 +155,6 @@ def test_emulated_kernels_match_oracle(oracle, emul, field_bits, layout, log_h, 
     assert np.array_equal(back, src)
 
 
-@pytest.mark.parametrize("field_bits,layout,log_h,log_rate", [
-    (32, 0, 16, 0), (128, 0, 14, 0), (128, 0, 16, 1), (32, 0, 18, 0), (128, 1, 16, 0), (32, 0, 20, 0), (128, 0, 18, 1), (32, 0, 22, 0)])
-def test_emulated_warp_owned_upper_passes(oracle, emul, field_bits, layout, log_h, log_rate):
-    """schedule 4: the upper passes as warp-owned 128-line groups (b2_wupper.cu; k = 2, 4 and 6) over the tile pass"""
-    limbs = field_bits // 32
-    x = _rand((1 << log_h) * limbs, 31 * log_h + log_rate)
-    src = oracle.bitslice(x, field_bits) if layout else x
-    out = np.zeros((1 << (log_h + log_rate)) * limbs, dtype=np.uint32)
-    assert emul.emul_antt_sched(field_bits, layout, log_h, log_rate, 1, src, out, 0, 0, 0, 0, 4) == 0
-    got = oracle.unbitslice(out, field_bits) if layout else out
-    assert np.array_equal(got, oracle.antt_forward(x, log_h, log_rate, limbs))
-    n = (1 << log_h) * limbs
-    back = np.zeros(n, dtype=np.uint32)
-    assert emul.emul_antt_sched(field_bits, layout, log_h, log_rate, 1, np.ascontiguousarray(out[:n]), back, 1, 0, 0, 0, 4) == 0
-    assert np.array_equal(back, src)
-
-
 def test_plan_constants_and_products_match_oracle(oracle, emul):
     for log_h, log_rate in [(20, 0), (20, 2), (28, 0), (28, 4)]:
         c = np.zeros(32 * 32, dtype=np.uint32)
