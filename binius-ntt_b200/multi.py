@@ -111,6 +111,13 @@ class FourStepNTT:
         self.full_plan = api.Plan(self.field_bits, self.log_n, 0, layout=self.layout, device=dev) if self.g else None
         self.local_plan = api.Plan(self.field_bits, self.log_local, self.g, layout=self.layout, device=dev)
 
+    @property
+    def launches(self):
+        """kernel launches of one forward(): top phase + local transform (the exchange is the collective library's)"""
+        return (self.full_plan.launches if self.full_plan else 0) + self.local_plan.launches
+
+    exchange_kind = "NCCL all_to_all_single between the two local phases"
+
     def top(self, buf, stream=None):
         """phase 1 on this rank's G segments (h, m = rank, .), in place."""
         if self.g:
@@ -129,10 +136,10 @@ class FourStepNTT:
         if self.world == 1:
             out.copy_(buf)
             return out
-        try:
-            dist.all_to_all_single(out, buf, group=self.group)
-        except (RuntimeError, NotImplementedError):
-            # backends without alltoall (old gloo): pairwise sends
+        if dist.get_backend(self.group) != "gloo":
+            dist.all_to_all_single(out, buf, group=self.group)  # errors of the collective propagate
+        else:
+            # gloo has no all-to-all on every build (CPU tests): pairwise sends
             ins = list(buf.view(self.world, -1).unbind(0))
             outs = list(out.view(self.world, -1).unbind(0))
             outs[self.rank].copy_(ins[self.rank])
@@ -151,9 +158,12 @@ class FourStepNTT:
         when not given); `buf` is overwritten by phase 1."""
         if buf.numel() != self.local_words:
             raise ValueError(f"FourStepNTT.forward: expected {self.local_words} words, got {buf.numel()}")
+        if buf.is_cuda and stream is not None and stream != torch.cuda.current_stream(buf.device):
+            # the collective is ordered against torch's CURRENT stream: make `stream` current for all three steps, so that
+            # the exchange waits for phase 1, phase 2 waits for the exchange and `scratch` is allocated on the same stream
+            with torch.cuda.stream(stream):
+                return self.forward(buf, scratch, stream)
         self.top(buf, stream)
-        if buf.is_cuda and stream is not None:
-            stream.synchronize()  # the collective runs on the backend's own stream
         out = self.exchange(buf, scratch)
         return self.local(out, stream)
 
