@@ -9,11 +9,14 @@ from .api import (  # noqa: F401
     B2NTTError,
     AdditiveNTT,
     AdditiveNTTConf,
+    BabyBearNTT,
     DataOrder,
     NTTData,
     GeneralNTT,
     Plan,
     Sumcheck,
+    bb31_decode,
+    bb31_encode,
     bitslice_,
     check_gpu_capabilities,
     lib,

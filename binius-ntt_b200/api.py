@@ -61,6 +61,11 @@ def lib():
         L.b2ntt_general_destroy.argtypes = [vp]
         L.b2ntt_general_exec.argtypes = [vp, vp, vp, i, vp]
         L.b2ntt_general_constants.argtypes = [vp, vp]
+        L.b2ntt_bb31_create.argtypes = [C.POINTER(vp), C.c_uint32, i, i, i]
+        L.b2ntt_bb31_destroy.argtypes = [vp]
+        L.b2ntt_bb31_exec.argtypes = [vp, vp, vp, i, vp]
+        L.b2ntt_bb31_exec_host.argtypes = [vp, vp, sz, i, vp]
+        L.b2ntt_bb31_launches.argtypes = [vp]
         L.b2ntt_sumcheck_launches.restype = C.c_longlong
         L.b2ntt_strerror.argtypes = [i]
         L.b2ntt_strerror.restype = C.c_char_p
@@ -328,6 +333,65 @@ class GeneralNTT:
             d_out = d_in
         Plan._dev_ok(self, d_out, self.words, "d_out")
         _check(lib().b2ntt_general_exec(self._h, d_in.data_ptr(), d_out.data_ptr(), int(inverse), _stream_ptr(stream)), "b2ntt_general_exec")
+        return d_out
+
+
+BB31_P = 15 * (1 << 27) + 1
+_BB31_R = (1 << 32) % BB31_P
+_BB31_RINV = pow(_BB31_R, BB31_P - 2, BB31_P)
+
+
+def bb31_encode(x):
+    """canonical residues (any uint32 is reduced first, as BB31(uint32_t) does) -> risc0::Fp raw words (Montgomery form)"""
+    return ((np.asarray(x, dtype=np.uint64) % BB31_P) * _BB31_R % BB31_P).astype(np.uint32)
+
+
+def bb31_decode(raw):
+    """risc0::Fp raw words -> canonical residues (Fp::asUInt32)"""
+    return (np.asarray(raw, dtype=np.uint64) * _BB31_RINV % BB31_P).astype(np.uint32)
+
+
+class BabyBearNTT:
+    """NTT<BB31> with NTTConfRad2<BB31>(generator, log_group_order, log_inp_size) (ntt/gpuntt.cuh:126-209,
+    ntt/nttconf.cuh:25-47) over b2ntt_bb31_*.  `apply` takes and returns CANONICAL residues as numpy uint32 (the C ABI and
+    `exec` move risc0::Fp raw words, the memory image of a BB31 array)."""
+
+    def __init__(self, log_inp_size, generator=137, log_group_order=27, device=0):
+        self._h = C.c_void_p()
+        gen_raw = int(bb31_encode(np.array([generator], dtype=np.uint32))[0])
+        _check(lib().b2ntt_bb31_create(C.byref(self._h), gen_raw, log_group_order, log_inp_size, device), "b2ntt_bb31_create")
+        self.log_n, self.device, self.in_words = log_inp_size, device, 1 << log_inp_size
+
+    def close(self):
+        if self._h:
+            lib().b2ntt_bb31_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def launches(self):
+        return lib().b2ntt_bb31_launches(self._h)
+
+    def apply(self, x, bit_reversed=False):
+        raw = np.ascontiguousarray(bb31_encode(x))
+        out = np.empty_like(raw)
+        _check(lib().b2ntt_bb31_exec_host(self._h, raw.ctypes.data, raw.size, int(bit_reversed), out.ctypes.data), "b2ntt_bb31_exec_host")
+        return bb31_decode(out)
+
+    def exec(self, d_in, d_out=None, bit_reversed=False, stream=None):
+        """device tensors of raw words; out of place unless the input is already bit-reversed"""
+        import torch
+
+        Plan._dev_ok(self, d_in, self.in_words, "d_in")
+        if d_out is None:
+            d_out = d_in if bit_reversed else torch.empty_like(d_in)
+        Plan._dev_ok(self, d_out, self.in_words, "d_out")
+        _check(lib().b2ntt_bb31_exec(self._h, d_in.data_ptr(), d_out.data_ptr(), int(bit_reversed), _stream_ptr(stream)), "b2ntt_bb31_exec")
         return d_out
 
 

@@ -163,6 +163,21 @@ int b2ntt_general_exec(b2ntt_general* g, const void* d_in, void* d_out, int inve
  * [log_h][log_h] elements of 4 words, row i holding log_h - 1 - i entries (rest zero). */
 int b2ntt_general_constants(const b2ntt_general* g, uint32_t* h_out);
 
+/* ---- BabyBear (p = 15 * 2^27 + 1) radix-2 NTT ----
+ * Replaces NTT<BB31> (ntt/gpuntt.cuh:126-209) with its configuration NTTConfRad2<BB31> (ntt/nttconf.cuh:25-47), its
+ * kernels ntt_kernel (gpuntt.cuh:65-124) and bit_reverse_in_place_ker (:22-34).  Words are risc0::Fp RAW values
+ * (Montgomery form, R = 2^32; finite_fields/risc0_baby_bear.h:163-177), i.e. the memory image of a BB31 array; the
+ * generator is given the same way.  1 <= log_n <= 27, log_group_order >= log_n (nttconf.cuh:32-39).
+ * Output = the reference's: an IN_ORDER input is bit-reversed first, then stages 0 .. log_n-1 of u + v, (u - v) * w. */
+typedef struct b2ntt_bb31 b2ntt_bb31;
+int b2ntt_bb31_create(b2ntt_bb31** out, uint32_t generator_raw, int log_group_order, int log_n, int device);
+int b2ntt_bb31_destroy(b2ntt_bb31* h);
+/* device-resident, asynchronous on `stream`; d_out may equal d_in only when the input is already bit-reversed */
+int b2ntt_bb31_exec(b2ntt_bb31* h, const void* d_in, void* d_out, int input_bit_reversed, void* stream);
+/* NTT<E>::apply (gpuntt.cuh:158-183): host in (n = 2^log_n elements), host out, synchronous */
+int b2ntt_bb31_exec_host(b2ntt_bb31* h, const void* h_in, size_t n, int input_bit_reversed, void* h_out);
+int b2ntt_bb31_launches(const b2ntt_bb31* h);
+
 const char* b2ntt_strerror(int code);
 /* Text of the last CUDA error seen by the calling thread's last failing call ("" if none). */
 const char* b2ntt_last_cuda_error(void);

@@ -36,5 +36,6 @@ inline void report_cuda(cudaError_t status, const char* file, int line, const ch
 constexpr int MAX_SHARED_MEM = 32 * 1024;     // bytes of static shared memory the reference kernels assumed
 constexpr int MAX_STAGES_PER_KERNEL = 11;     // not consulted by the pass scheduler
 
-// utils/common.cu:6-43 -- device 0, true when the device can run the library
-inline bool check_gpu_capabilities() { return b2ntt_check_gpu_capabilities(0) > 0; }
+// utils/common.cu:6-43 -- device 0, true when the device can run the library.  A compiled symbol of ulvt_gpu, as in the
+// reference (defined in csrc/b2_compat.cu over b2ntt_check_gpu_capabilities).
+bool check_gpu_capabilities();

@@ -57,6 +57,11 @@ void orc_unbitslice(uint32_t* block, int width_bits); /* inverse */
  * finite_fields/circuit_generator/multiply_and_generate_circuit.cpp:62-155) */
 void orc_mul_bitsliced(const uint32_t* a, const uint32_t* b, uint32_t* out, int h);
 
+/* ---- BabyBear radix-2 NTT (ntt/gpuntt.cuh:12-209), canonical residues, bb31.c ---- */
+uint32_t orc_bb31_mul(uint32_t a, uint32_t b);
+uint32_t orc_bb31_pow(uint32_t x, uint64_t n);
+int orc_bb31_ntt(const uint32_t* in, uint32_t* out, int log_n, uint32_t generator, int log_group_order, int input_bit_reversed);
+
 /* ---- additive NTT (ntt/additive_ntt.cuh) ---- */
 /* normalised subspace-polynomial constants C[i][j], i < log_h, j < log_h+log_rate-1-i, row pitch
  * = log_h+log_rate-1 words (additive_ntt.cuh:273-309).  Returns the pitch. */

@@ -58,6 +58,12 @@ def _load():
     lib.orc_antt_general_direct.argtypes = [_u32p, _u32p, C.c_int, C.c_void_p]
     lib.orc_antt_general_direct.restype = C.c_int
     lib.orc_md5_hex.argtypes = [C.c_void_p, C.c_size_t, C.c_char_p]
+    lib.orc_bb31_mul.argtypes = [C.c_uint32, C.c_uint32]
+    lib.orc_bb31_mul.restype = C.c_uint32
+    lib.orc_bb31_pow.argtypes = [C.c_uint32, C.c_uint64]
+    lib.orc_bb31_pow.restype = C.c_uint32
+    lib.orc_bb31_ntt.argtypes = [_u32p, _u32p, C.c_int, C.c_uint32, C.c_int, C.c_int]
+    lib.orc_bb31_ntt.restype = C.c_int
     lib.orc_mt19937_fill.argtypes = [C.c_uint32, _u32p, C.c_size_t]
     lib.orc_golden_md5.argtypes = [C.c_int, C.c_int]
     lib.orc_golden_md5.restype = C.c_char_p
@@ -190,6 +196,19 @@ def antt_inverse(y: np.ndarray, log_h: int, log_rate: int = 0, coset: int = 0, l
     rc = lib.orc_antt_inverse(y, out, log_h, log_rate, coset, limbs, threads)
     if rc:
         raise ValueError("bad arguments")
+    return out
+
+
+BB31_P = 15 * (1 << 27) + 1
+
+
+def bb31_ntt(x, log_n, generator=137, log_group_order=27, input_bit_reversed=False):
+    """BabyBear radix-2 NTT of ntt/gpuntt.cuh:126-209 on canonical residues (the reference stores Montgomery words)."""
+    x = np.ascontiguousarray(x, dtype=np.uint32)
+    out = np.empty(1 << log_n, dtype=np.uint32)
+    rc = lib.orc_bb31_ntt(x, out, log_n, generator, log_group_order, 1 if input_bit_reversed else 0)
+    if rc:
+        raise ValueError(f"orc_bb31_ntt: {rc}")
     return out
 
 

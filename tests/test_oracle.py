@@ -115,6 +115,22 @@ def test_oracle_matches_reference_host_code(oracle):
     assert np.array_equal(out, oracle.mul128(a, b).reshape(-1))
 
 
+def test_bb31_oracle_matches_reference_digests(oracle):
+    """the BabyBear NTT restatement (oracle/bb31.c) against bb31_ntt_hashes (ntt/tests/test_ntt.cu:21-50)"""
+    import hashlib
+    import json
+
+    gold = json.load(open(os.path.join(ROOT, "tests", "golden", "bb31_ntt_md5.json")))["md5"]
+    for log_len in range(1, 21):
+        out = oracle.bb31_ntt(oracle.mt19937(0xDEADBEEF + log_len, 1 << log_len), log_len)
+        assert hashlib.md5(out.tobytes()).hexdigest() == gold[str(log_len)], log_len
+    # the inverse generator undoes the transform up to the factor n (test_ntt.cu:152-187)
+    P, L = oracle.BB31_P, 10
+    x = _rand(1 << L, 3) % np.uint32(P)
+    y = oracle.bb31_ntt(oracle.bb31_ntt(x, L), L, pow(137, P - 2, P))
+    assert np.array_equal((y.astype(np.uint64) * pow(1 << L, P - 2, P) % P).astype(np.uint32), x)
+
+
 # ---- CPU emulation of the CUDA pass phases (same source as the kernels) -------------------------------
 @pytest.fixture(scope="module")
 def emul():

@@ -11,7 +11,8 @@ BIN = os.path.join(ROOT, "tests", "cpp", "shim_test")
 
 
 def test_shim_headers_exist_and_cite_the_reference():
-    for rel, cite in [("ulvt/ntt/additive_ntt.cuh", "additive_ntt.cuh:176-270"), ("ulvt/ntt/nttconf.cuh", "nttconf.cuh:9-60"),
+    for rel, cite in [("ulvt/ntt/additive_ntt.cuh", "additive_ntt.cuh:176-270"), ("ulvt/ntt/nttconf.cuh", "nttconf.cuh:9-114"), ("ulvt/ntt/gpuntt.cuh", "gpuntt.cuh:126-209"),
+                      ("ulvt/finite_fields/baby_bear.cuh", "risc0_baby_bear.h:40-187"),
                       ("ulvt/finite_fields/binary_tower.cuh", "binary_tower.cuh:19-262"), ("ulvt/utils/bitslicing.cuh", "bitslicing.cuh:8-104"),
                       ("ulvt/utils/common.cuh", "common.cuh:3-32"), ("ulvt/sumcheck/sumcheck.cuh", "sumcheck/sumcheck.cuh:10-300"),
                       ("ulvt/finite_fields/circuit_generator/unrolled/binary_tower_unrolled.cuh", "binary_tower_unrolled.cuh:4-5"),
