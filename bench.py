@@ -324,17 +324,22 @@ def bench_four_step(b2, dev, stream, world, rank, dist, iters=3):
     log_s = 22
     g = torch.Generator(device=dev).manual_seed(1234)  # the same stream on every rank
     x = torch.randint(-2**31, 2**31 - 1, ((1 << log_s) * 4,), dtype=torch.int32, device=dev, generator=g)
-    fs = b2.FourStepNTT(log_s, 128, device=dev.index)
-    out = fs.forward(b2.FourStepNTT.m_shard(x, world, rank, 4).contiguous().clone())
     whole = b2.Plan(128, log_s, 0, device=dev.index)
     ref = whole.exec(x.clone())
-    ok = bool(torch.equal(out, ref[rank * fs.local_words:(rank + 1) * fs.local_words]))
-    Launches.n += whole.launches + fs.launches
-    fs.close(), whole.close()
+    ok = True
+    for fused in (True, False):  # both exchange paths against the single-GPU transform
+        fs = b2.FourStepNTT(log_s, 128, device=dev.index, fused=fused)
+        out = fs.forward(b2.FourStepNTT.m_shard(x, world, rank, 4).contiguous().clone())
+        ok = ok and bool(torch.equal(out, ref[rank * fs.local_words:(rank + 1) * fs.local_words]))
+        Launches.n += fs.launches
+        fs.close()
+    Launches.n += whole.launches
+    whole.close()
     del x, ref, out
     bad = max_of(0.0 if ok else 1.0)
     log_n = min(30, 27 + int(math.log2(world)))
-    fs = b2.FourStepNTT(log_n, 128, device=dev.index)
+    # -- A/B baseline: phase 1 in place, NCCL all_to_all_single, phase 2
+    fs = b2.FourStepNTT(log_n, 128, device=dev.index, fused=False)
     buf = torch.randint(-2**31, 2**31 - 1, (fs.local_words,), dtype=torch.int32, device=dev)
     scratch = torch.empty_like(buf)
     for _ in range(2):
@@ -358,13 +363,41 @@ def bench_four_step(b2, dev, stream, world, rank, dist, iters=3):
         whole_ms += e[0].elapsed_time(e[3]) / iters
     Launches.n += (2 + iters) * fs.launches
     ms = [max_of(t) for t in tot]
-    total = max_of(whole_ms)
-    res = {"log_n": log_n, "ms": total, "value": (1 << log_n) / total * 1e3, "unit": UNIT, "ms_top": ms[0], "ms_exchange": ms[1], "ms_local": ms[2],
-           "exchange": fs.exchange_kind, "exchange_bytes_per_gpu_each_way": fs.local_words * 4 * (world - 1) // world,
-           "exchange_GBps_per_gpu": fs.local_words * 4 * (world - 1) / world / ms[1] / 1e6, "timing": "max over ranks, CUDA events per phase",
-           "verified": bad == 0.0, "check": f"log_n={log_s}: every rank's block == the same block of a single-GPU transform of the whole input"}
+    nccl_total = max_of(whole_ms)
+    bytes_each_way = fs.local_words * 4 * (world - 1) // world
+    nccl = {"ms": nccl_total, "ms_top": ms[0], "ms_exchange": ms[1], "ms_local": ms[2], "exchange": fs.exchange_kind,
+            "exchange_GBps_per_gpu": bytes_each_way / ms[1] / 1e6}
     fs.close()
-    del buf, scratch
+    del scratch
+    # -- the product path: exchange fused into the phase-1 kernel's peer stores
+    fs = b2.FourStepNTT(log_n, 128, device=dev.index, fused=True)
+    for _ in range(2):
+        fs.forward(buf)
+    torch.cuda.synchronize()
+    dist.barrier()
+    t_sc = t_lo = t_all = 0.0
+    for _ in range(iters):
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        e[0].record(stream)
+        fs._stream_barrier()
+        fs.scatter(buf)
+        fs._stream_barrier()
+        e[1].record(stream)
+        fs.local(fs.block)
+        e[2].record(stream)
+        torch.cuda.synchronize()
+        t_sc += e[0].elapsed_time(e[1]) / iters
+        t_lo += e[1].elapsed_time(e[2]) / iters
+        t_all += e[0].elapsed_time(e[2]) / iters
+    Launches.n += (2 + iters) * fs.launches
+    t_sc, t_lo, total = max_of(t_sc), max_of(t_lo), max_of(t_all)
+    res = {"log_n": log_n, "ms": total, "value": (1 << log_n) / total * 1e3, "unit": UNIT, "ms_scatter": t_sc, "ms_local": t_lo,
+           "ms_exchange_exposed": max(0.0, t_sc - ms[0]), "exchange": fs.exchange_kind, "exchange_bytes_per_gpu_each_way": bytes_each_way,
+           "scatter_GBps_per_gpu": bytes_each_way / t_sc / 1e6, "nccl_baseline": nccl, "timing": "max over ranks, CUDA events per phase; "
+           "ms_scatter spans barrier + phase-1 kernel with peer stores + barrier; ms_exchange_exposed = ms_scatter - the baseline's ms_top",
+           "verified": bad == 0.0, "check": f"log_n={log_s}, both exchange paths: every rank's block == the same block of a single-GPU transform of the whole input"}
+    fs.close()
+    del buf
     torch.cuda.empty_cache()
     return res
 

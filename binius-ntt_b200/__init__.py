@@ -13,6 +13,7 @@ from .api import (  # noqa: F401
     DataOrder,
     NTTData,
     GeneralNTT,
+    MultiGPU,
     Plan,
     Sumcheck,
     bb31_decode,

@@ -61,6 +61,21 @@ def lib():
         L.b2ntt_general_destroy.argtypes = [vp]
         L.b2ntt_general_exec.argtypes = [vp, vp, vp, i, vp]
         L.b2ntt_general_constants.argtypes = [vp, vp]
+        L.b2ntt_fourstep_create.argtypes = [C.POINTER(vp), i, i, i, i, i]
+        L.b2ntt_fourstep_destroy.argtypes = [vp]
+        L.b2ntt_fourstep_block_bytes.argtypes = [vp]
+        L.b2ntt_fourstep_block_bytes.restype = sz
+        L.b2ntt_fourstep_launches.argtypes = [vp]
+        L.b2ntt_fourstep_set_peer.argtypes = [vp, i, vp]
+        L.b2ntt_fourstep_scatter.argtypes = [vp, vp, vp]
+        L.b2ntt_fourstep_local.argtypes = [vp, vp, vp]
+        L.b2ntt_ipc_export.argtypes = [vp, vp, C.POINTER(sz)]
+        L.b2ntt_ipc_open.argtypes = [vp, sz, i, C.POINTER(vp)]
+        L.b2ntt_ipc_close.argtypes = [vp, sz, i]
+        L.b2ntt_mg_create.argtypes = [C.POINTER(vp), i, i, C.POINTER(i), i, i, i, i]
+        L.b2ntt_mg_columns.argtypes = [vp, i, C.POINTER(i), C.POINTER(i)]
+        L.b2ntt_mg_exec.argtypes = [vp, C.POINTER(vp), C.POINTER(vp)]
+        L.b2ntt_mg_destroy.argtypes = [vp]
         L.b2ntt_bb31_create.argtypes = [C.POINTER(vp), C.c_uint32, i, i, i]
         L.b2ntt_bb31_destroy.argtypes = [vp]
         L.b2ntt_bb31_exec.argtypes = [vp, vp, vp, i, vp]
@@ -334,6 +349,49 @@ class GeneralNTT:
         Plan._dev_ok(self, d_out, self.words, "d_out")
         _check(lib().b2ntt_general_exec(self._h, d_in.data_ptr(), d_out.data_ptr(), int(inverse), _stream_ptr(stream)), "b2ntt_general_exec")
         return d_out
+
+
+MG_COLUMN_SHARD, MG_FOUR_STEP = 0, 1
+
+
+class MultiGPU:
+    """b2ntt_mg: ONE process driving several GPUs of the box.  mode MG_COLUMN_SHARD: `batch` independent columns
+    in contiguous slabs per device, no traffic between devices; mode MG_FOUR_STEP: one transform of 2^log_h elements split over
+    the devices, the exchange fused into the first phase's peer stores.  exec takes one device tensor per GPU and blocks."""
+
+    def __init__(self, mode, devices, field_bits, log_h, log_rate=0, batch=1):
+        self._h = C.c_void_p()
+        devs = (C.c_int * len(devices))(*devices)
+        _check(lib().b2ntt_mg_create(C.byref(self._h), mode, len(devices), devs, field_bits, log_h, log_rate, batch), "b2ntt_mg_create")
+        self.mode, self.devices, self.limbs = mode, list(devices), field_bits // 32
+
+    def columns(self, i):
+        first, count = C.c_int(), C.c_int()
+        _check(lib().b2ntt_mg_columns(self._h, i, C.byref(first), C.byref(count)), "b2ntt_mg_columns")
+        return first.value, count.value
+
+    def exec(self, d_ins, d_outs):
+        n = len(self.devices)
+        if len(d_ins) != n or len(d_outs) != n:
+            raise ValueError("MultiGPU.exec: one input and one output tensor per device")
+        for t, d in zip(list(d_ins) + list(d_outs), self.devices * 2):
+            if t is not None and (not t.is_cuda or t.device.index != d or not t.is_contiguous()):
+                raise ValueError("MultiGPU.exec: tensor i must be contiguous on devices[i]")
+        pin = (C.c_void_p * n)(*[t.data_ptr() if t is not None else None for t in d_ins])
+        pout = (C.c_void_p * n)(*[t.data_ptr() if t is not None else None for t in d_outs])
+        _check(lib().b2ntt_mg_exec(self._h, pin, pout), "b2ntt_mg_exec")
+        return d_outs
+
+    def close(self):
+        if self._h:
+            lib().b2ntt_mg_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 BB31_P = 15 * (1 << 27) + 1

@@ -65,6 +65,11 @@ struct PassParams {
 	uint64_t n_tiles;   // rows << (nb - k)
 	uint64_t n_groups;  // ceil(n_tiles / (2T >> k))
 	uint8_t cls[32];    // per layer: 0 = twiddle is always 0, else log2 of the twiddle subfield bits (2..5)
+	// Top phase of a transform split over 2^k devices with the exchange fused into the store: line (x, lo) of the
+	// pass output goes to device x's block buffer, slot scatter_rank, line lo -- 16-byte stores into peer memory over NVLink.
+	int scatter_n;         // 0: ordinary pass; else 2^k = number of destination buffers
+	int scatter_rank;      // this device's slot in every destination block
+	uint32_t* scatter[16]; // destination block of device x (mapped in this process: peer access or CUDA IPC)
 };
 
 struct Bundles {
@@ -217,6 +222,19 @@ template <bool STORE>
 B2_HD void group_copy(const PassParams& P, PassSmem& sm, uint64_t group, int tid) {
 	const int T = P.cta_threads;
 	const int ltpg = P.log_tpg, tpg = 1 << ltpg;
+	if (STORE && P.scatter_n) {
+		// fused exchange: the tile's line x belongs to device x (the pass owns the top line bits of the local buffer, hi = 0)
+#pragma unroll 1
+		for (int c = tid; c < 8 * P.group_lines; c += T) {
+			const int piece = c & 7, r = c >> 3;
+			const int tig = r & (tpg - 1), x = r >> ltpg;
+			const TileCoord tc = tile_coord_of(P, group, tig);
+			if (!tc.active) continue;
+			const uint64_t off = ((((uint64_t)P.scatter_rank << P.q0) | tc.lo) << 5) + piece * 4;
+			copy16_s2g(P.scatter[x] + (uint64_t)tc.row * P.dst_row_words + off, &sm.slots[slot_word(tc.slot_base + x, piece * 4)]);
+		}
+		return;
+	}
 	if (8 * tpg <= T) {
 		const int piece = tid & 7, r0 = tid >> 3;
 		const TileCoord tc = tile_coord_of(P, group, r0 & (tpg - 1));

@@ -271,7 +271,8 @@ inline void plan_fill_bottom(const HostPlan& hp, BottomParams& B, int n, const u
 // stages (global stages log_h-1 .. log_h-log_seg) in place, element-wise across the segments: their
 // twiddles depend only on the h bits above the butterfly bit, which the local index keeps on top.
 // hp is the plan of the FULL transform (log_rate 0, compact or bit-sliced images).  Returns 0 or -1.
-inline int plan_fill_top(const HostPlan& hp, PassParams& P, int log_seg, uint32_t* buf, const uint32_t* consts, const uint32_t* lane_tw) {
+inline int plan_fill_top(const HostPlan& hp, PassParams& P, int log_seg, uint32_t* buf, const uint32_t* consts, const uint32_t* lane_tw,
+                         void* const* scatter = nullptr, int scatter_rank = 0) {
 	if (hp.log_rate != 0 || log_seg < 1 || log_seg > 4) return -1;
 	const int nb_local = hp.nb - log_seg;                     // line bits of the local buffer
 	const int q0 = nb_local - log_seg;                        // the segment-index bits are its top bits
@@ -293,6 +294,10 @@ inline int plan_fill_top(const HostPlan& hp, PassParams& P, int log_seg, uint32_
 	const uint64_t tpg = (uint64_t)hp.group_lines >> log_seg;
 	P.n_groups = (P.n_tiles + tpg - 1) / tpg;
 	memcpy(P.cls, hp.cls, 32);
+	if (scatter) {  // results leave for the devices' block buffers instead of going back to `buf`
+		P.scatter_n = 1 << log_seg, P.scatter_rank = scatter_rank;
+		for (int x = 0; x < P.scatter_n; x++) P.scatter[x] = (uint32_t*)scatter[x];
+	}
 	return 0;
 }
 

@@ -361,3 +361,231 @@ extern "C" const char* b2ntt_strerror(int code) {
 	}
 }
 extern "C" const char* b2ntt_last_cuda_error(void) { return g_cuda_err; }
+
+// ================================================================================================================================
+// Multi-GPU: one transform split over 2^g devices with the exchange fused into the first phase's stores, and
+// the single-process drivers b2ntt_mg_* for a C++ caller that owns all the GPUs of the box.
+// ================================================================================================================================
+struct b2ntt_fourstep {
+	b2ntt_plan* full = nullptr;   // plan of the whole transform: constants and classes of the top g stages
+	b2ntt_plan* local = nullptr;  // (log_h = log_n - g, log_rate = g): phase 2 is its coset `rank`
+	int g = 0, rank = 0, device = 0, log_n = 0, field_bits = 0;
+	void* peers[16] = {};         // block buffer of every rank, mapped in this process
+};
+
+extern "C" int b2ntt_fourstep_create(b2ntt_fourstep** out, int field_bits, int log_n, int log_ranks, int rank, int device) {
+	if (!out) return B2NTT_EINVAL;
+	*out = nullptr;
+	if (log_ranks < 0 || log_ranks > 4 || rank < 0 || rank >= (1 << log_ranks) || log_n - 2 * log_ranks < 1) return B2NTT_EINVAL;
+	const int limbs_log = field_bits == 128 ? 2 : 0;
+	if (log_ranks && log_n - 2 * log_ranks + limbs_log < 5) return B2NTT_EINVAL;  // a segment is at least one 128-byte line
+	b2ntt_fourstep* fs = new (std::nothrow) b2ntt_fourstep;
+	if (!fs) return B2NTT_ENOMEM;
+	fs->g = log_ranks, fs->rank = rank, fs->device = device, fs->log_n = log_n, fs->field_bits = field_bits;
+	int rc = log_ranks ? b2ntt_plan_create(&fs->full, field_bits, B2NTT_LAYOUT_COMPACT, log_n, 0, 1, device) : B2NTT_OK;
+	if (rc == B2NTT_OK) rc = b2ntt_plan_create(&fs->local, field_bits, B2NTT_LAYOUT_COMPACT, log_n - log_ranks, log_ranks, 1, device);
+	if (rc != B2NTT_OK) {
+		b2ntt_plan_destroy(fs->full), b2ntt_plan_destroy(fs->local);
+		delete fs;
+		return rc;
+	}
+	*out = fs;
+	return B2NTT_OK;
+}
+extern "C" int b2ntt_fourstep_destroy(b2ntt_fourstep* fs) {
+	if (!fs) return B2NTT_OK;
+	b2ntt_plan_destroy(fs->full), b2ntt_plan_destroy(fs->local);
+	delete fs;
+	return B2NTT_OK;
+}
+extern "C" size_t b2ntt_fourstep_block_bytes(const b2ntt_fourstep* fs) {
+	return fs ? ((size_t)(fs->field_bits / 8) << (fs->log_n - fs->g)) : 0;
+}
+extern "C" int b2ntt_fourstep_launches(const b2ntt_fourstep* fs) {
+	return fs ? (fs->g ? 1 : 0) + b2ntt_plan_launches(fs->local) : B2NTT_EINVAL;
+}
+extern "C" int b2ntt_fourstep_set_peer(b2ntt_fourstep* fs, int peer_rank, void* d_block) {
+	if (!fs || peer_rank < 0 || peer_rank >= (1 << fs->g) || !d_block) return B2NTT_EINVAL;
+	fs->peers[peer_rank] = d_block;
+	return B2NTT_OK;
+}
+// Phase 1 + exchange: the top g stages across this rank's 2^g segments (h, m = rank, .), segment h stored straight into rank
+// h's block buffer at slot `rank`.  d_shard is read only.  Every rank's block must be free of readers (a barrier before).
+extern "C" int b2ntt_fourstep_scatter(b2ntt_fourstep* fs, const void* d_shard, void* stream) {
+	if (!fs || !d_shard) return B2NTT_EINVAL;
+	for (int r = 0; r < (1 << fs->g); r++)
+		if (!fs->peers[r]) return B2NTT_EINVAL;
+	if (pointer_device(d_shard) != fs->device) return B2NTT_EINVAL;
+	DeviceGuard guard(fs->device);
+	CU(guard.err);
+	if (fs->g == 0) {
+		if (fs->peers[0] != d_shard) CU(cudaMemcpyAsync(fs->peers[0], d_shard, b2ntt_fourstep_block_bytes(fs), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+		return B2NTT_OK;
+	}
+	PassParams P;
+	b2ntt_plan* p = fs->full;
+	if (p->hp.tiny || plan_fill_top(p->hp, P, fs->g, (uint32_t*)d_shard, p->d_consts, p->d_lane_tw, fs->peers, fs->rank)) return B2NTT_EINVAL;
+	if (launch_pass(P, (cudaStream_t)stream)) return cuda_fail(cudaGetLastError(), "launch_pass (scatter)");
+	return B2NTT_OK;
+}
+// Phase 2: the local transform of the block this rank owns, in place (needs every rank's scatter to have completed).
+extern "C" int b2ntt_fourstep_local(b2ntt_fourstep* fs, void* d_block, void* stream) {
+	if (!fs || !d_block) return B2NTT_EINVAL;
+	return run(fs->local, d_block, d_block, false, fs->rank, (cudaStream_t)stream, true);
+}
+
+// ---- CUDA IPC helpers for one-process-per-GPU callers (torchrun): export a device buffer, map a peer's --------------------
+extern "C" int b2ntt_ipc_export(const void* d_ptr, void* handle64, size_t* offset) {
+	if (!d_ptr || !handle64 || !offset) return B2NTT_EINVAL;
+	static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+	const int dev = pointer_device(d_ptr);
+	if (dev < 0) return B2NTT_EINVAL;
+	DeviceGuard guard(dev);
+	CU(guard.err);
+	// base of the allocation that holds d_ptr: cuMemGetAddressRange of the driver API, looked up at run time (the library
+	// does not link libcuda, so it still loads on a machine without a driver)
+	typedef int (*range_fn)(unsigned long long*, size_t*, unsigned long long);
+	void* fn = nullptr;
+	cudaDriverEntryPointQueryResult qres;
+	CU(cudaGetDriverEntryPoint("cuMemGetAddressRange", &fn, cudaEnableDefault, &qres));
+	if (!fn || qres != cudaDriverEntryPointSuccess) return B2NTT_EUNSUPPORTED;
+	unsigned long long base_addr = 0;
+	size_t size = 0;
+	if (((range_fn)fn)(&base_addr, &size, (unsigned long long)(uintptr_t)d_ptr) != 0) return cuda_fail(cudaErrorInvalidValue, "cuMemGetAddressRange");
+	void* base = (void*)(uintptr_t)base_addr;
+	CU(cudaIpcGetMemHandle((cudaIpcMemHandle_t*)handle64, base));
+	*offset = (size_t)((const char*)d_ptr - (const char*)base);
+	return B2NTT_OK;
+}
+extern "C" int b2ntt_ipc_open(const void* handle64, size_t offset, int device, void** d_ptr) {
+	if (!handle64 || !d_ptr) return B2NTT_EINVAL;
+	DeviceGuard guard(device);
+	CU(guard.err);
+	void* base = nullptr;
+	cudaIpcMemHandle_t h;
+	memcpy(&h, handle64, sizeof h);
+	CU(cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
+	*d_ptr = (char*)base + offset;
+	return B2NTT_OK;
+}
+extern "C" int b2ntt_ipc_close(void* d_ptr, size_t offset, int device) {
+	if (!d_ptr) return B2NTT_OK;
+	DeviceGuard guard(device);
+	CU(guard.err);
+	CU(cudaIpcCloseMemHandle((char*)d_ptr - offset));
+	return B2NTT_OK;
+}
+
+// ---- single-process drivers: one host thread, one stream per device -------------------------------------------------------------
+struct b2ntt_mg {
+	int mode = 0, n = 0, field_bits = 0, log_h = 0, log_rate = 0, batch = 0;
+	int devices[16] = {};
+	cudaStream_t streams[16] = {};
+	cudaEvent_t ev_scatter[16] = {};
+	b2ntt_plan* plans[16] = {};      // COLUMN_SHARD: device i transforms columns [first[i], first[i] + count[i])
+	int first[16] = {}, count[16] = {};
+	b2ntt_fourstep* fs[16] = {};     // FOUR_STEP
+};
+
+extern "C" int b2ntt_mg_destroy(b2ntt_mg* mg) {
+	if (!mg) return B2NTT_OK;
+	for (int i = 0; i < mg->n; i++) {
+		DeviceGuard guard(mg->devices[i]);
+		if (mg->streams[i]) cudaStreamDestroy(mg->streams[i]);
+		if (mg->ev_scatter[i]) cudaEventDestroy(mg->ev_scatter[i]);
+		b2ntt_plan_destroy(mg->plans[i]);
+		b2ntt_fourstep_destroy(mg->fs[i]);
+	}
+	delete mg;
+	return B2NTT_OK;
+}
+
+extern "C" int b2ntt_mg_create(b2ntt_mg** out, int mode, int n_gpus, const int* devices, int field_bits, int log_h, int log_rate, int batch) {
+	if (!out) return B2NTT_EINVAL;
+	*out = nullptr;
+	if (!devices || n_gpus < 1 || n_gpus > 16 || (mode != B2NTT_MG_COLUMN_SHARD && mode != B2NTT_MG_FOUR_STEP)) return B2NTT_EINVAL;
+	int g = 0;
+	while ((1 << g) < n_gpus) g++;
+	if (mode == B2NTT_MG_FOUR_STEP && ((1 << g) != n_gpus || log_rate != 0 || batch != 1)) return B2NTT_EINVAL;
+	if (mode == B2NTT_MG_COLUMN_SHARD && batch < 1) return B2NTT_EINVAL;
+	for (int i = 0; i < n_gpus; i++)
+		for (int j = 0; j < i; j++)
+			if (devices[i] == devices[j]) return B2NTT_EINVAL;
+	b2ntt_mg* mg = new (std::nothrow) b2ntt_mg;
+	if (!mg) return B2NTT_ENOMEM;
+	mg->mode = mode, mg->n = n_gpus, mg->field_bits = field_bits, mg->log_h = log_h, mg->log_rate = log_rate, mg->batch = batch;
+	int rc = B2NTT_OK;
+	for (int i = 0; i < n_gpus && rc == B2NTT_OK; i++) {
+		mg->devices[i] = devices[i];
+		DeviceGuard guard(devices[i]);
+		if (guard.err != cudaSuccess || cudaStreamCreateWithFlags(&mg->streams[i], cudaStreamNonBlocking) != cudaSuccess ||
+		    cudaEventCreateWithFlags(&mg->ev_scatter[i], cudaEventDisableTiming) != cudaSuccess) {
+			rc = cuda_fail(cudaGetLastError(), "b2ntt_mg_create");
+			break;
+		}
+		if (mode == B2NTT_MG_COLUMN_SHARD) {
+			// contiguous slabs of columns, sizes differing by at most one
+			const int base = batch / n_gpus, extra = batch % n_gpus;
+			mg->first[i] = i * base + (i < extra ? i : extra), mg->count[i] = base + (i < extra ? 1 : 0);
+			if (mg->count[i]) rc = b2ntt_plan_create(&mg->plans[i], field_bits, B2NTT_LAYOUT_COMPACT, log_h, log_rate, mg->count[i], devices[i]);
+		} else {
+			rc = b2ntt_fourstep_create(&mg->fs[i], field_bits, log_h, g, i, devices[i]);
+			for (int j = 0; j < n_gpus && rc == B2NTT_OK; j++) {  // the scatter stores into every other device's block
+				if (j == i) continue;
+				int can = 0;
+				cudaDeviceCanAccessPeer(&can, devices[i], devices[j]);
+				if (!can) {
+					rc = B2NTT_EUNSUPPORTED;
+					break;
+				}
+				const cudaError_t e = cudaDeviceEnablePeerAccess(devices[j], 0);
+				if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) rc = cuda_fail(e, "cudaDeviceEnablePeerAccess");
+				cudaGetLastError();
+			}
+		}
+	}
+	if (rc != B2NTT_OK) {
+		b2ntt_mg_destroy(mg);
+		return rc;
+	}
+	*out = mg;
+	return B2NTT_OK;
+}
+
+extern "C" int b2ntt_mg_columns(const b2ntt_mg* mg, int i, int* first, int* count) {
+	if (!mg || i < 0 || i >= mg->n || mg->mode != B2NTT_MG_COLUMN_SHARD) return B2NTT_EINVAL;
+	if (first) *first = mg->first[i];
+	if (count) *count = mg->count[i];
+	return B2NTT_OK;
+}
+
+// Launches on every device, then waits for all of them.  COLUMN_SHARD: d_in[i] / d_out[i] = device i's columns (no data moves
+// between devices).  FOUR_STEP: d_in[i] = rank i's m-shard (2^g segments (h, m = i, .), read only), d_out[i] = block i of the
+// transform in natural order; the only cross-device traffic is the scatter's peer stores.
+extern "C" int b2ntt_mg_exec(b2ntt_mg* mg, void* const* d_in, void* const* d_out) {
+	if (!mg || !d_in || !d_out) return B2NTT_EINVAL;
+	int rc = B2NTT_OK;
+	if (mg->mode == B2NTT_MG_COLUMN_SHARD) {
+		for (int i = 0; i < mg->n && rc == B2NTT_OK; i++)
+			if (mg->plans[i]) rc = b2ntt_exec(mg->plans[i], d_in[i], d_out[i], mg->streams[i]);
+	} else {
+		for (int i = 0; i < mg->n && rc == B2NTT_OK; i++)
+			for (int j = 0; j < mg->n && rc == B2NTT_OK; j++) rc = b2ntt_fourstep_set_peer(mg->fs[i], j, d_out[j]);
+		for (int i = 0; i < mg->n && rc == B2NTT_OK; i++) {
+			rc = b2ntt_fourstep_scatter(mg->fs[i], d_in[i], mg->streams[i]);
+			DeviceGuard guard(mg->devices[i]);
+			if (rc == B2NTT_OK && cudaEventRecord(mg->ev_scatter[i], mg->streams[i]) != cudaSuccess) rc = cuda_fail(cudaGetLastError(), "cudaEventRecord");
+		}
+		for (int i = 0; i < mg->n && rc == B2NTT_OK; i++) {
+			DeviceGuard guard(mg->devices[i]);
+			for (int j = 0; j < mg->n; j++)  // block i is complete when every device's scatter has finished
+				if (cudaStreamWaitEvent(mg->streams[i], mg->ev_scatter[j], 0) != cudaSuccess) rc = cuda_fail(cudaGetLastError(), "cudaStreamWaitEvent");
+			if (rc == B2NTT_OK) rc = b2ntt_fourstep_local(mg->fs[i], d_out[i], mg->streams[i]);
+		}
+	}
+	for (int i = 0; i < mg->n; i++) {  // drain every stream even after an error: no launch outlives the call
+		DeviceGuard guard(mg->devices[i]);
+		if (cudaStreamSynchronize(mg->streams[i]) != cudaSuccess && rc == B2NTT_OK) rc = cuda_fail(cudaGetLastError(), "cudaStreamSynchronize");
+	}
+	return rc;
+}

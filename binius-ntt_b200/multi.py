@@ -17,6 +17,10 @@ are libb2ntt.so calls (include/b2ntt.h).
              transform whose twiddle block index is offset by h, i.e. coset h of a
              (log_h = log_n - g, log_rate = g) plan                  -> b2ntt_exec_coset
   Output: natural order, block-sharded (rank h holds block h).
+  Two exchange paths: `fused` (default on CUDA with more than one rank) = b2ntt_fourstep_scatter, the phase-1
+  kernel stores segment h straight into rank h's block with 16-byte peer stores (blocks mapped across the
+  processes by CUDA IPC, two stream-ordered barriers per transform, no collective on the data path);
+  otherwise phase 1 in place + NCCL all_to_all_single (the A/B baseline, and gloo on the CPU tests).
 """
 import torch
 import torch.distributed as dist
@@ -84,8 +88,10 @@ class FourStepNTT:
     """One additive NTT of 2^log_n elements split over G = 2^g ranks (config 4: log_n = 30, GF(2^128),
     G = 8: 2 GiB per rank)."""
 
-    def __init__(self, log_n, field_bits=128, layout=api.LAYOUT_COMPACT, group=None, device=None):
+    def __init__(self, log_n, field_bits=128, layout=api.LAYOUT_COMPACT, group=None, device=None, fused=None):
         self.group = group
+        self._fs = None
+        self._fused_req = fused
         self.world, self.rank = _world_rank(group)
         g = self.world.bit_length() - 1
         if self.world != 1 << g:
@@ -110,6 +116,59 @@ class FourStepNTT:
         self.device = dev
         self.full_plan = api.Plan(self.field_bits, self.log_n, 0, layout=self.layout, device=dev) if self.g else None
         self.local_plan = api.Plan(self.field_bits, self.log_local, self.g, layout=self.layout, device=dev)
+        want = self._fused_req
+        if want is None:
+            want = self.g > 0 and dist.is_initialized() and dist.get_backend(self.group) == "nccl"
+        if want:
+            self._setup_fused(dev)
+
+    def _setup_fused(self, dev):
+        """Map every rank's block buffer into this process (CUDA IPC) and create the b2ntt_fourstep object."""
+        import ctypes as C
+
+        L = api.lib()
+        self._fs = C.c_void_p()
+        api._check(L.b2ntt_fourstep_create(C.byref(self._fs), self.field_bits, self.log_n, self.g, self.rank, dev), "b2ntt_fourstep_create")
+        self.block = torch.empty(self.local_words, dtype=torch.int32, device=torch.device("cuda", dev))
+        handle, off = (C.c_ubyte * 64)(), C.c_size_t()
+        api._check(L.b2ntt_ipc_export(self.block.data_ptr(), handle, C.byref(off)), "b2ntt_ipc_export")
+        mine = (bytes(handle), off.value)
+        everyone = [None] * self.world
+        dist.all_gather_object(everyone, mine, group=self.group)
+        self._opened = []
+        for r, (h, o) in enumerate(everyone):
+            if r == self.rank:
+                ptr = C.c_void_p(self.block.data_ptr())
+            else:
+                ptr = C.c_void_p()
+                api._check(L.b2ntt_ipc_open((C.c_ubyte * 64).from_buffer_copy(h), o, dev, C.byref(ptr)), "b2ntt_ipc_open")
+                self._opened.append((ptr, o))
+            api._check(L.b2ntt_fourstep_set_peer(self._fs, r, ptr), "b2ntt_fourstep_set_peer")
+        self._flag = torch.zeros(1, dtype=torch.int32, device=self.block.device)
+        self.exchange_kind = "fused: phase-1 kernel stores into the peers' blocks (16-byte stores over NVLink, CUDA IPC), no collective"
+
+    def _stream_barrier(self):
+        """all ranks' work enqueued so far on the current stream is complete before anything enqueued after it starts"""
+        dist.all_reduce(self._flag, group=self.group)
+
+    def scatter(self, buf, stream=None):
+        """phase 1 + exchange, fused: reads this rank's m-shard, fills every rank's block"""
+        api._check(api.lib().b2ntt_fourstep_scatter(self._fs, buf.data_ptr(), api._stream_ptr(stream)), "b2ntt_fourstep_scatter")
+
+    def forward_fused(self, buf):
+        """buf: this rank's m-shard (left untouched).  Returns self.block = block `rank` of the transform.  Runs on torch's
+        current stream; the two barriers are tiny all-reduces ordered on that stream."""
+        if buf.numel() != self.local_words:
+            raise ValueError(f"FourStepNTT.forward: expected {self.local_words} words, got {buf.numel()}")
+        self._stream_barrier()   # nobody still reads the block of the previous transform
+        self.scatter(buf)
+        self._stream_barrier()   # every rank's stores have landed
+        api._check(api.lib().b2ntt_fourstep_local(self._fs, self.block.data_ptr(), api._stream_ptr(None)), "b2ntt_fourstep_local")
+        return self.block
+
+    @property
+    def fused(self):
+        return self._fs is not None
 
     @property
     def launches(self):
@@ -158,6 +217,8 @@ class FourStepNTT:
         when not given); `buf` is overwritten by phase 1."""
         if buf.numel() != self.local_words:
             raise ValueError(f"FourStepNTT.forward: expected {self.local_words} words, got {buf.numel()}")
+        if self._fs is not None and scratch is None and stream is None:
+            return self.forward_fused(buf)
         if buf.is_cuda and stream is not None and stream != torch.cuda.current_stream(buf.device):
             # the collective is ordered against torch's CURRENT stream: make `stream` current for all three steps, so that
             # the exchange waits for phase 1, phase 2 waits for the exchange and `scratch` is allocated on the same stream
@@ -177,6 +238,14 @@ class FourStepNTT:
         return x_global.reshape(world, world, -1)[:, rank, :].reshape(-1)
 
     def close(self):
+        if self._fs is not None:
+            torch.cuda.synchronize()
+            if dist.is_initialized():
+                dist.barrier(group=self.group)  # no peer still stores into this rank's block
+            for ptr, off in self._opened:
+                api.lib().b2ntt_ipc_close(ptr, off, self.device)
+            api.lib().b2ntt_fourstep_destroy(self._fs)
+            self._fs = None
         for p in (getattr(self, "full_plan", None), getattr(self, "local_plan", None)):
             if p:
                 p.close()

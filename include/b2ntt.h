@@ -163,6 +163,43 @@ int b2ntt_general_exec(b2ntt_general* g, const void* d_in, void* d_out, int inve
  * [log_h][log_h] elements of 4 words, row i holding log_h - 1 - i entries (rest zero). */
 int b2ntt_general_constants(const b2ntt_general* g, uint32_t* h_out);
 
+/* ---- multi-GPU on one NVLink / NVSwitch box (no reference counterpart: the reference is single-GPU) ----
+ * ONE transform of 2^log_n elements over 2^log_ranks devices ("four-step", BASELINE config 4).  Global index
+ * i = (h : g bits, m : g bits, l).  Rank m starts with the 2^g segments (h, m, .) ("m-shard") and ends with the contiguous
+ * block [m * 2^(log_n-g), ...) of the transform in natural order.  The reference runs its layers from the highest stride down
+ * (additive_ntt.cuh:233-247), so there is exactly one exchange, and it is FUSED into phase 1: the kernel that runs the top g
+ * layers stores segment h straight into rank h's block buffer with 16-byte peer stores over NVLink (no collective call).
+ * One object per rank; the ranks may live in one process (peer access) or in one process each (CUDA IPC, helpers below).
+ * Caller's protocol per transform: [all blocks free of readers] -> scatter on every rank -> [every scatter complete] ->
+ * local on every rank.  b2ntt_mg_exec does this with events; a torchrun caller uses two stream-ordered barriers. */
+typedef struct b2ntt_fourstep b2ntt_fourstep;
+int b2ntt_fourstep_create(b2ntt_fourstep** fs, int field_bits, int log_n, int log_ranks, int rank, int device);
+int b2ntt_fourstep_destroy(b2ntt_fourstep* fs);
+size_t b2ntt_fourstep_block_bytes(const b2ntt_fourstep* fs);   /* bytes of a rank's shard = of its block */
+int b2ntt_fourstep_launches(const b2ntt_fourstep* fs);
+/* d_block = rank peer_rank's block buffer as mapped in THIS process (all 2^log_ranks of them, the own one included) */
+int b2ntt_fourstep_set_peer(b2ntt_fourstep* fs, int peer_rank, void* d_block);
+int b2ntt_fourstep_scatter(b2ntt_fourstep* fs, const void* d_shard, void* stream);   /* phase 1 + exchange; d_shard is read only */
+int b2ntt_fourstep_local(b2ntt_fourstep* fs, void* d_block, void* stream);           /* phase 2, in place on the own block */
+/* CUDA IPC for one-process-per-GPU callers: handle64 = 64 bytes (cudaIpcMemHandle_t of the allocation that holds d_ptr),
+ * offset = d_ptr's offset inside it; open maps it into the calling process on `device` (peer access enabled lazily). */
+int b2ntt_ipc_export(const void* d_ptr, void* handle64, size_t* offset);
+int b2ntt_ipc_open(const void* handle64, size_t offset, int device, void** d_ptr);
+int b2ntt_ipc_close(void* d_ptr, size_t offset, int device);
+
+/* Single-process drivers for a caller that owns all the GPUs (b2ntt_mg_create / exec / destroy).
+ * B2NTT_MG_COLUMN_SHARD (config 3): `batch` independent columns of (log_h, log_rate), contiguous slabs per device
+ * (b2ntt_mg_columns), no data moves between devices.  B2NTT_MG_FOUR_STEP (config 4): log_rate = 0, batch = 1, n_gpus a power
+ * of two; d_in[i] = rank i's m-shard (read only), d_out[i] = block i.  exec launches on one stream per device and returns
+ * when every device has finished. */
+#define B2NTT_MG_COLUMN_SHARD 0
+#define B2NTT_MG_FOUR_STEP 1
+typedef struct b2ntt_mg b2ntt_mg;
+int b2ntt_mg_create(b2ntt_mg** mg, int mode, int n_gpus, const int* devices, int field_bits, int log_h, int log_rate, int batch);
+int b2ntt_mg_columns(const b2ntt_mg* mg, int i, int* first, int* count);
+int b2ntt_mg_exec(b2ntt_mg* mg, void* const* d_in, void* const* d_out);
+int b2ntt_mg_destroy(b2ntt_mg* mg);
+
 /* ---- BabyBear (p = 15 * 2^27 + 1) radix-2 NTT ----
  * Replaces NTT<BB31> (ntt/gpuntt.cuh:126-209) with its configuration NTTConfRad2<BB31> (ntt/nttconf.cuh:25-47), its
  * kernels ntt_kernel (gpuntt.cuh:65-124) and bit_reverse_in_place_ker (:22-34).  Words are risc0::Fp RAW values

@@ -21,6 +21,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--log-n", type=int, default=28)
     ap.add_argument("--iters", type=int, default=3)
+    ap.add_argument("--parity-only", action="store_true", help="item 1 only (both exchange paths): the leg tests/test_multi_gpu.py runs")
     args = ap.parse_args()
     rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(lr)
@@ -30,21 +31,29 @@ def main():
     log_s = 22
     g = torch.Generator(device=dev).manual_seed(1234)  # same stream on every rank
     x = torch.randint(-2**31, 2**31 - 1, ((1 << log_s) * 4,), dtype=torch.int32, device=dev, generator=g)
-    fs = b2.FourStepNTT(log_s, 128)
-    mine = b2.FourStepNTT.m_shard(x, world, rank, 4).contiguous().clone()
-    out = fs.forward(mine)
     whole = b2.Plan(128, log_s, 0, device=lr)
     ref = whole.exec(x.clone())
-    n = fs.local_words
-    ok = bool(torch.equal(out, ref[rank * n:(rank + 1) * n]))
-    flags = [None] * world
-    dist.all_gather_object(flags, ok)
-    if rank == 0:
-        print(json.dumps({"check": "four_step_parity", "log_n": log_s, "world": world, "all_blocks_equal": all(flags)}), flush=True)
-    fs.close(), whole.close()
+    for fused in (True, False):
+        fs = b2.FourStepNTT(log_s, 128, fused=fused)
+        mine = b2.FourStepNTT.m_shard(x, world, rank, 4).contiguous().clone()
+        out = fs.forward(mine)
+        n = fs.local_words
+        ok = bool(torch.equal(out, ref[rank * n:(rank + 1) * n]))
+        if fused:  # a second transform through the same object: the block is reused behind the barriers
+            ok = ok and bool(torch.equal(fs.forward(mine), ref[rank * n:(rank + 1) * n]))
+        flags = [None] * world
+        dist.all_gather_object(flags, ok)
+        if rank == 0:
+            print(json.dumps({"check": "four_step_parity", "exchange": "fused peer stores" if fused else "nccl all_to_all", "log_n": log_s, "world": world,
+                              "all_blocks_equal": all(flags)}), flush=True)
+        fs.close()
+    whole.close()
     del x, ref, out, mine
+    if args.parity_only:
+        dist.destroy_process_group()
+        return
     # ---- 2. config 4 timing ----------------------------------------------------------------------------
-    fs = b2.FourStepNTT(args.log_n, 128)
+    fs = b2.FourStepNTT(args.log_n, 128, fused=False)
     buf = torch.randint(-2**31, 2**31 - 1, (fs.local_words,), dtype=torch.int32, device=dev)
     scratch = torch.empty_like(buf)
     stream = torch.cuda.current_stream()
