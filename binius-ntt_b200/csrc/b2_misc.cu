@@ -4,9 +4,11 @@
 // kernels of finite_fields/tests/test_kernels.cu:9-60 and bitsliced_repeat
 // (finite_fields/tests/profiling/kernels/bitsliced_repeat.cu:6-33).
 #include <cuda_runtime.h>
+#include <stdlib.h>
 
 #include "b2_bundle.cuh"
 #include "b2_launch.h"
+#include "b2_pass.cuh"
 #include "b2_mul128.cuh"
 
 namespace b2 {
@@ -231,6 +233,135 @@ __global__ void __launch_bounds__(kMulThreads, B2_MUL128_CTAS) mul_sliced128_ker
 	}
 }
 
+// ---- bit-sliced GF(2^128), warp-owned form (config 5) --------------------------------------------------------------------------
+// A warp owns 32 consecutive blocks, lane = block, and runs all nine GF(2^32) products of its blocks itself: no CTA barrier, no
+// operand staging.  The operand of product j is a subset sum of the block's four limbs; the nine subsets are visited along a
+// Gray path ({0} {01} {1} {13} {3} {23} {2} {02} {0123}), so x and y change by ONE limb (read straight from global memory /
+// L1, 8 x 16 bytes per thread) between products instead of being rebuilt.  Each product is XORed into the lane's private
+// result row in shared memory (4 limbs x 32 words, pitch 132: conflict-free 16-byte accesses), which the warp then stores
+// coalesced.  With a5 = the GF(2^32)-level alpha (A below) the result limbs are
+//   L0 = P0+P1+P3+P4                      L1 = P0+P1+P2+P3+P4+P5 + A(P1+P4)
+//   L2 = P0+P1+P5+P6+P7 + A P4            L3 = P0+P1+P2+P5+P6+P7+P8 + A(P1+P3+P5+P7) + A A P4
+// (P0 = a0 b0, P1 = a1 b1, P2 = (a0+a1)(b0+b1), P3..P5 the same on limbs 2, 3, P6..P8 on the sums a0+a2, a1+a3: two Karatsuba
+// levels over GF(2^32), multiply_unrolled<7>, finite_fields/circuit_generator/unrolled/binary_tower_unrolled.cuh:4-5).
+constexpr int kWMulWarps = 8, kWMulPitch = 132, kWStagePitch = 36;
+constexpr int kWMulWarpWords = 32 * kWMulPitch + 2 * 32 * kWStagePitch;  // result rows + one staged limb of a and of b
+constexpr size_t kWMulSmemBytes = (size_t)kWMulWarps * kWMulWarpWords * sizeof(uint32_t);
+
+__device__ __forceinline__ void xor_limb(const uint32_t* g, uint32_t* w) {  // w ^= the 32 words at g
+	const uint4* q = reinterpret_cast<const uint4*>(g);
+#pragma unroll
+	for (int i = 0; i < 8; i++) {
+		const uint4 u = q[i];
+		w[4 * i] ^= u.x, w[4 * i + 1] ^= u.y, w[4 * i + 2] ^= u.z, w[4 * i + 3] ^= u.w;
+	}
+}
+template <bool FIRST>
+__device__ __forceinline__ void acc_limb(uint32_t* row, const uint32_t* v) {  // row (^)= v
+	uint4* q = reinterpret_cast<uint4*>(row);
+#pragma unroll
+	for (int i = 0; i < 8; i++) {
+		uint4 u = make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+		if (!FIRST) {
+			const uint4 o = q[i];
+			u.x ^= o.x, u.y ^= o.y, u.z ^= o.z, u.w ^= o.w;
+		}
+		q[i] = u;
+	}
+}
+// limb `limb` of the 32 blocks starting at block `first`, of both operands, into the warp's staging rows: coalesced 16-byte
+// cp.async, four 128-byte rows per warp instruction; rows past nact are not touched
+__device__ __forceinline__ void stage_limb(uint32_t* sta, uint32_t* stb, const uint32_t* a, const uint32_t* b, uint64_t first, int nact, int limb, int lane) {
+	const int piece = lane & 7, r4 = lane >> 3;
+#pragma unroll
+	for (int it = 0; it < 8; it++) {
+		const int r = it * 4 + r4;
+		if (r < nact) {
+			const uint64_t off = (first + r) * 128 + 32 * limb + piece * 4;
+			copy16_g2s(sta + r * kWStagePitch + piece * 4, a + off);
+			copy16_g2s(stb + r * kWStagePitch + piece * 4, b + off);
+		}
+	}
+	asm volatile("cp.async.commit_group;" ::: "memory");
+}
+
+__global__ void __launch_bounds__(kWMulWarps * 32, 1) mul_sliced128_warp_kernel(const uint32_t* a, const uint32_t* b, uint32_t* o, uint64_t n_blocks) {
+	extern __shared__ __align__(16) uint32_t wsm[];
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	uint32_t* rows = wsm + (size_t)warp * kWMulWarpWords;
+	uint32_t *sta = rows + 32 * kWMulPitch, *stb = sta + 32 * kWStagePitch;
+	uint32_t* row = rows + lane * kWMulPitch;  // this lane's result block
+	const uint64_t n_sets = (n_blocks + 31) / 32, stride = (uint64_t)gridDim.x * kWMulWarps;
+	uint64_t set = (uint64_t)blockIdx.x * kWMulWarps + warp;
+	if (set < n_sets) stage_limb(sta, stb, a, b, set * 32, n_blocks - set * 32 < 32 ? (int)(n_blocks - set * 32) : 32, 0, lane);
+	for (; set < n_sets; set += stride) {
+		const uint64_t first = set * 32;
+		const int nact = n_blocks - first < 32 ? (int)(n_blocks - first) : 32;
+		const bool act = lane < nact;
+		uint32_t x[32], y[32], t[32], q[32];
+#pragma unroll
+		for (int i = 0; i < 32; i++) x[i] = 0, y[i] = 0;
+		// The limbs arrive in the order 0 1 0 3 1 2 3 0 1 3 (one toggle of the Gray path each, the last subset needs two); a
+		// product follows every arrival but the ninth.  ONE product call site walked nine times: nine inlined copies of the
+		// circuit spill and thrash the instruction cache.  The next limb (or limb 0 of the warp's next 32 blocks) is copied in
+		// while the product runs.
+		// step:            P0      P2      P1      P7      P4      P5      P3      P6      P8
+		// t        -> limbs 0123   13      02      2       0       12      01      23      3
+		// t + A t  -> limbs -      -       13      3       1       3       -       -       -
+		// A t      -> limbs -      -       -       -       2       -       3       -       -
+		// A A t    -> limbs -      -       -       -       3       -       -       -       -
+		const uint64_t order = 0x3103213010ull;  // nibble i = limb of arrival i
+		const uint64_t tm = 0x8C36145AFull, rm = 0x828A00ull, qm = 0x8040000ull, am = 0x80000ull;  // nibble per step, bit l = limb l
+#pragma unroll 1
+		for (int i = 0; i < 10; i++) {
+			asm volatile("cp.async.wait_group 0;" ::: "memory");
+			__syncwarp();
+			if (act) xor_limb(sta + lane * kWStagePitch, x), xor_limb(stb + lane * kWStagePitch, y);
+			__syncwarp();  // the staging rows are free again
+			if (i < 9)
+				stage_limb(sta, stb, a, b, first, nact, (int)((order >> (4 * (i + 1))) & 15), lane);
+			else if (set + stride < n_sets)
+				stage_limb(sta, stb, a, b, (set + stride) * 32, n_blocks - (set + stride) * 32 < 32 ? (int)(n_blocks - (set + stride) * 32) : 32, 0, lane);
+			if (i == 8 || !act) continue;
+			const int st = i < 8 ? i : 8;
+			Sliced<5>::mul(x, y, t);
+			const int mt = (int)((tm >> (4 * st)) & 15), mr = (int)((rm >> (4 * st)) & 15), mq = (int)((qm >> (4 * st)) & 15), ma = (int)((am >> (4 * st)) & 15);
+#pragma unroll 1
+			for (int l = 0; l < 4; l++)
+				if ((mt >> l) & 1) {
+					if (st == 0)
+						acc_limb<true>(row + 32 * l, t);
+					else
+						acc_limb<false>(row + 32 * l, t);
+				}
+			if (mr | mq | ma) {
+				Sliced<5>::mul_alpha(t, q);
+#pragma unroll 1
+				for (int l = 0; l < 4; l++)
+					if ((mq >> l) & 1) acc_limb<false>(row + 32 * l, q);
+				if (mr) {
+#pragma unroll
+					for (int k = 0; k < 32; k++) t[k] ^= q[k];
+#pragma unroll 1
+					for (int l = 0; l < 4; l++)
+						if ((mr >> l) & 1) acc_limb<false>(row + 32 * l, t);
+				}
+				if (ma) {
+					Sliced<5>::mul_alpha(q, t);
+#pragma unroll 1
+					for (int l = 0; l < 4; l++)
+						if ((ma >> l) & 1) acc_limb<false>(row + 32 * l, t);
+				}
+			}
+		}
+		__syncwarp();  // every lane has finished its row; all operand reads of this set are done (o may alias a or b)
+#pragma unroll 4
+		for (int r = 0; r < nact; r++)  // one block (512 bytes) per warp instruction
+			*reinterpret_cast<uint4*>(o + (first + r) * 128 + lane * 4) = *reinterpret_cast<const uint4*>(rows + r * kWMulPitch + lane * 4);
+		__syncwarp();
+	}
+}
+
 int launch_mul(int field_bits, int layout, const uint32_t* a, const uint32_t* b, uint32_t* o, uint64_t n, cudaStream_t stream) {
 	if (n == 0) return 0;
 	const unsigned cap = 148 * 16;
@@ -263,10 +394,19 @@ int launch_mul(int field_bits, int layout, const uint32_t* a, const uint32_t* b,
 			if (blocks > cap) blocks = cap;
 			mul_sliced32_kernel<<<blocks, 128, 0, stream>>>(a, b, o, nb);
 		} else if (field_bits == 128) {
-			unsigned blocks = (unsigned)((nb + 31) / 32);
-			if (blocks > cap) blocks = cap;
-			cudaFuncSetAttribute(mul_sliced128_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMulSmemBytes);
-			mul_sliced128_kernel<false><<<blocks, kMulThreads, kMulSmemBytes, stream>>>(a, b, o, nb, nb * 32);
+			static const int form = getenv("B2NTT_MUL128") ? atoi(getenv("B2NTT_MUL128")) : 1;  // 0: CTA-level product (A/B), 1: warp-owned
+			if (form == 1) {
+				const uint64_t sets = (nb + 31) / 32;
+				unsigned blocks = (unsigned)((sets + kWMulWarps - 1) / kWMulWarps);
+				if (blocks > 148 * 4) blocks = 148 * 4;
+				cudaFuncSetAttribute(mul_sliced128_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWMulSmemBytes);
+				mul_sliced128_warp_kernel<<<blocks, kWMulWarps * 32, kWMulSmemBytes, stream>>>(a, b, o, nb);
+			} else {
+				unsigned blocks = (unsigned)((nb + 31) / 32);
+				if (blocks > cap) blocks = cap;
+				cudaFuncSetAttribute(mul_sliced128_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMulSmemBytes);
+				mul_sliced128_kernel<false><<<blocks, kMulThreads, kMulSmemBytes, stream>>>(a, b, o, nb, nb * 32);
+			}
 		} else
 			return -1;
 	}
