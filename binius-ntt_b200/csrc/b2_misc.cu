@@ -428,10 +428,79 @@ __global__ void __launch_bounds__(128) mul_repeat32_kernel(uint32_t* io, uint64_
 	for (int i = 0; i < 8; i++) po[i] = make_uint4(x[4 * i], x[4 * i + 1], x[4 * i + 2], x[4 * i + 3]);
 }
 
+// GF(2^128) form of the probe: x <- x * y on lane-private rows of shared memory (a 128-word operand does not fit a thread's
+// registers), the nine GF(2^32) products of every step through the same single call site as mul_sliced128_warp_kernel
+__device__ __forceinline__ void lane_mul128(const uint32_t* xa, const uint32_t* yb, uint32_t* row) {
+	uint32_t x[32], y[32], t[32], q[32];
+#pragma unroll
+	for (int i = 0; i < 32; i++) x[i] = 0, y[i] = 0;
+	const uint64_t order = 0x3103213010ull, tm = 0x8C36145AFull, rm = 0x828A00ull, qm = 0x8040000ull, am = 0x80000ull;
+#pragma unroll 1
+	for (int i = 0; i < 10; i++) {
+		const int limb = (int)((order >> (4 * i)) & 15);
+		xor_limb(xa + 32 * limb, x), xor_limb(yb + 32 * limb, y);
+		if (i == 8) continue;
+		const int st = i < 8 ? i : 8;
+		Sliced<5>::mul(x, y, t);
+		const int mt = (int)((tm >> (4 * st)) & 15), mr = (int)((rm >> (4 * st)) & 15), mq = (int)((qm >> (4 * st)) & 15), ma = (int)((am >> (4 * st)) & 15);
+#pragma unroll 1
+		for (int l = 0; l < 4; l++)
+			if ((mt >> l) & 1) {
+				if (st == 0)
+					acc_limb<true>(row + 32 * l, t);
+				else
+					acc_limb<false>(row + 32 * l, t);
+			}
+		if (mr | mq | ma) {
+			Sliced<5>::mul_alpha(t, q);
+#pragma unroll 1
+			for (int l = 0; l < 4; l++)
+				if ((mq >> l) & 1) acc_limb<false>(row + 32 * l, q);
+			if (mr) {
+#pragma unroll
+				for (int k = 0; k < 32; k++) t[k] ^= q[k];
+#pragma unroll 1
+				for (int l = 0; l < 4; l++)
+					if ((mr >> l) & 1) acc_limb<false>(row + 32 * l, t);
+			}
+			if (ma) {
+				Sliced<5>::mul_alpha(q, t);
+#pragma unroll 1
+				for (int l = 0; l < 4; l++)
+					if ((ma >> l) & 1) acc_limb<false>(row + 32 * l, t);
+			}
+		}
+	}
+}
+constexpr int kRep128Threads = 128;
+constexpr size_t kRep128SmemBytes = (size_t)3 * kRep128Threads * kWMulPitch * sizeof(uint32_t);
+// thread g owns the 128-word block g of io: x = the block, y = x with its limbs rotated and a constant mixed in
+__global__ void __launch_bounds__(kRep128Threads, 1) mul_repeat128_kernel(uint32_t* io, uint64_t n_threads, int iters) {
+	extern __shared__ __align__(16) uint32_t rsm[];
+	const uint64_t g = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+	if (g >= n_threads) return;  // rows are thread-private: no barrier below
+	uint32_t* xr = rsm + (size_t)threadIdx.x * kWMulPitch;
+	uint32_t* yr = xr + (size_t)kRep128Threads * kWMulPitch;
+	uint32_t* zr = yr + (size_t)kRep128Threads * kWMulPitch;
+	for (int i = 0; i < 128; i++) xr[i] = io[g * 128 + i];
+	for (int i = 0; i < 128; i++) yr[i] = xr[(i + 33) & 127] ^ 0x9e3779b9u * (i + 1);
+#pragma unroll 1
+	for (int it = 0; it < iters; it++) {
+		lane_mul128(xr, yr, zr);
+		uint32_t* sw = xr;
+		xr = zr, zr = sw;
+	}
+	for (int i = 0; i < 128; i++) io[g * 128 + i] = xr[i];
+}
+
 int launch_mul_repeat(int field_bits, uint32_t* io, uint64_t n_threads, int iters, cudaStream_t stream) {
-	if (field_bits != 32) return -4;
+	if (field_bits != 32 && field_bits != 128) return -4;
 	if (n_threads == 0) return 0;
-	mul_repeat32_kernel<<<(unsigned)((n_threads + 127) / 128), 128, 0, stream>>>(io, n_threads, iters);
+	if (field_bits == 128) {
+		cudaFuncSetAttribute(mul_repeat128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRep128SmemBytes);
+		mul_repeat128_kernel<<<(unsigned)((n_threads + kRep128Threads - 1) / kRep128Threads), kRep128Threads, kRep128SmemBytes, stream>>>(io, n_threads, iters);
+	} else
+		mul_repeat32_kernel<<<(unsigned)((n_threads + 127) / 128), 128, 0, stream>>>(io, n_threads, iters);
 	return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 

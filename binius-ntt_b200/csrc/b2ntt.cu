@@ -330,7 +330,7 @@ extern "C" int b2ntt_mul(int field_bits, int layout, const void* a, const void* 
 }
 
 extern "C" int b2ntt_mul_repeat(int field_bits, void* d_io, size_t n_threads, int iters, void* stream) {
-	if (field_bits != 32) return field_bits == 128 ? B2NTT_EUNSUPPORTED : B2NTT_EINVAL;
+	if (field_bits != 32 && field_bits != 128) return B2NTT_EINVAL;
 	if (!d_io || iters < 0) return B2NTT_EINVAL;
 	const int dev = pointer_device(d_io);
 	if (dev < 0) return B2NTT_EINVAL;

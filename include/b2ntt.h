@@ -120,7 +120,10 @@ int b2ntt_mul(int field_bits, int layout, const void* d_a, const void* d_b, void
 
 /* Dependent-chain bit-sliced multiply microbenchmark: every thread squares-and-multiplies `iters`
  * times in registers (the shape of bitsliced_repeat, finite_fields/tests/profiling/kernels/
- * bitsliced_repeat.cu:6-33).  Used to measure the logic-pipe peak.  d_io: threads * 2^h words. */
+ * bitsliced_repeat.cu:6-33).  Used to measure the logic-pipe peak.  d_io: threads * 2^h words.
+ * field_bits 32: x <- x * y on 32-word operands in registers; 128: the same chain on 128-word blocks
+ * (multiply_unrolled<7> per step), operands in thread-private rows of shared memory.  In both forms
+ * y = the block's words rotated by 33 (32: by 1) and XORed with 0x9e3779b9 * (index + 1). */
 int b2ntt_mul_repeat(int field_bits, void* d_io, size_t n_threads, int iters, void* stream);
 
 /* Replaces bool check_gpu_capabilities() (utils/common.cu:6-43): 1 capable, 0 not, <0 error. */

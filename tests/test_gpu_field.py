@@ -186,3 +186,20 @@ def test_mul_in_place_aliasing(b2, oracle, cuda, field_bits, layout):
     sq = _host(b2.mul(da, da.clone(), field_bits, layout))
     b2.mul(da, da, field_bits, layout, out=da)
     assert np.array_equal(_host(da), sq)
+
+
+@pytest.mark.parametrize("field_bits,n_threads", [(32, 1), (32, 200), (128, 1), (128, 130)])
+def test_mul_repeat_vs_oracle(b2, oracle, cuda, field_bits, n_threads):
+    """the dependent-chain probe (bitsliced_repeat's shape, profiling/kernels/bitsliced_repeat.cu:6-33): x <- x * y, `iters`
+    times, in both widths; y = x's words rotated (by 1 / by 33) XOR 0x9e3779b9 * (index + 1), as include/b2ntt.h states"""
+    W, iters = field_bits, 3
+    x = _rand(n_threads * W, 9 + field_bits).reshape(n_threads, W)
+    rot = 1 if W == 32 else 33
+    idx = (np.arange(W) + rot) % W
+    y = x[:, idx] ^ (np.uint32(0x9E3779B9) * (np.arange(W, dtype=np.uint32) + np.uint32(1)))[None, :]
+    ref = x.copy()
+    for _ in range(iters):
+        ref = oracle.mul_bitsliced(ref.reshape(-1), np.ascontiguousarray(y).reshape(-1), 5 if W == 32 else 7).reshape(n_threads, W)
+    d = _dev(x.reshape(-1), cuda)
+    b2.mul_repeat(d, field_bits, iters)
+    assert np.array_equal(_host(d).reshape(n_threads, W), ref)
