@@ -57,6 +57,7 @@ def lib():
         L.b2ntt_sumcheck_next_round.argtypes = [vp, vp]
         L.b2ntt_sumcheck_round.argtypes = [vp]
         L.b2ntt_sumcheck_launches.argtypes = [vp]
+        L.b2ntt_sumcheck_set_recompute.argtypes = [vp, i]
         L.b2ntt_general_create.argtypes = [C.POINTER(vp), i, vp, i]
         L.b2ntt_general_destroy.argtypes = [vp]
         L.b2ntt_general_exec.argtypes = [vp, vp, vp, i, vp]
@@ -480,6 +481,10 @@ class Sumcheck:
             if h.size != words:
                 raise ValueError("Sumcheck: evals must hold composition_size * 2^num_vars * 4 32-bit words")
             _check(lib().b2ntt_sumcheck_load_host(self._h, h.ctypes.data, int(data_is_transposed)), "b2ntt_sumcheck_load_host")
+
+    def set_recompute(self, on=True):
+        """compute p(1) from the data in every device round and fail (B2NTT_ECHECK) if it differs from the derived value"""
+        _check(lib().b2ntt_sumcheck_set_recompute(self._h, int(on)), "b2ntt_sumcheck_set_recompute")
 
     def this_round_messages(self):
         """-> (sum[4], points[composition_size + 1][4]) as uint32 arrays"""

@@ -143,6 +143,7 @@ struct b2ntt_sumcheck {
 	int points_round = -1;    // round whose points are in last_points
 	gf128 claim{};            // q(r) of the round before the current one
 	bool have_claim = false;
+	bool recompute_p1 = false;  // b2ntt_sumcheck_set_recompute
 	bool loaded = false;
 	uint64_t launches = 0;
 };
@@ -289,7 +290,7 @@ extern "C" int b2ntt_sumcheck_round_messages(b2ntt_sumcheck* s, uint32_t* sum, u
 	uint64_t ctas = (half_rows + 31) / 32;
 	if (ctas > (uint64_t)s->sms * 2) ctas = (uint64_t)s->sms * 2;
 	const size_t smem = (kMulSmemWords + (C + 1) * 128) * sizeof(uint32_t);
-	const int skip1 = s->have_claim ? 1 : 0;
+	const int skip1 = (s->have_claim && !s->recompute_p1) ? 1 : 0;
 	sc_round_kernel<<<(unsigned)ctas, kMulThreads, smem>>>(s->d_evals, s->n0 * 4, half_rows, C, skip1, s->d_out);
 	SCU(cudaGetLastError());
 	s->launches++;
@@ -304,8 +305,17 @@ extern "C" int b2ntt_sumcheck_round_messages(b2ntt_sumcheck* s, uint32_t* sum, u
 	}
 	if (skip1)
 		for (int i = 0; i < 4; i++) points[4 + i] = s->claim.w[i] ^ points[i];
+	else if (s->have_claim)  // p(1) came from the data: it must agree with the verifier's claim
+		for (int i = 0; i < 4; i++)
+			if (points[4 + i] != (s->claim.w[i] ^ points[i])) return B2NTT_ECHECK;
 	for (int i = 0; i < 4; i++) sum[i] = points[i] ^ points[4 + i];
 	memcpy(s->last_points, points, (C + 1) * 16), s->points_round = s->round;
+	return B2NTT_OK;
+}
+
+extern "C" int b2ntt_sumcheck_set_recompute(b2ntt_sumcheck* s, int on) {
+	if (!s) return B2NTT_EINVAL;
+	s->recompute_p1 = on != 0;
 	return B2NTT_OK;
 }
 

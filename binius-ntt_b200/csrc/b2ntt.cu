@@ -178,8 +178,14 @@ extern "C" int b2ntt_exec_profile(b2ntt_plan* p, const void* d_in, void* d_out, 
 	if (np > max_passes || np > 15) return B2NTT_EINVAL;
 	DeviceGuard guard(p->device);
 	CU(guard.err);
-	cudaEvent_t ev[16];
-	for (int i = 0; i <= np; i++) CU(cudaEventCreate(&ev[i]));
+	cudaEvent_t ev[16] = {};
+	for (int i = 0; i <= np; i++) {
+		const cudaError_t e = cudaEventCreate(&ev[i]);
+		if (e != cudaSuccess) {
+			for (int k = 0; k < i; k++) cudaEventDestroy(ev[k]);
+			return cuda_fail(e, "cudaEventCreate");
+		}
+	}
 	int rc = run(p, d_in, d_out, false, 0, (cudaStream_t)stream, false, ev);
 	if (rc == B2NTT_OK && cudaEventSynchronize(ev[np]) != cudaSuccess) rc = cuda_fail(cudaGetLastError(), "cudaEventSynchronize");
 	for (int i = 0; i < np && rc == B2NTT_OK; i++) {
@@ -252,34 +258,44 @@ extern "C" int b2ntt_exec_host_batch(b2ntt_plan* p, const void* const* h_in, siz
 	const size_t ib = in_words(hp) * 4, ob = out_words(hp) * 4;
 	constexpr int K = b2ntt_plan::kPipe;
 	if (!p->pipe_ready) {
-		for (int i = 0; i < 3; i++) CU(cudaStreamCreateWithFlags(&p->ps[i], cudaStreamNonBlocking));
+		// every resource is created only if its handle is still null: a call that failed half-way (ENOMEM) is retried
+		// without leaking what the first attempt made; b2ntt_plan_destroy frees whatever exists
+		for (int i = 0; i < 3; i++)
+			if (!p->ps[i]) CU(cudaStreamCreateWithFlags(&p->ps[i], cudaStreamNonBlocking));
 		for (int i = 0; i < K; i++) {
-			cudaError_t e = cudaMalloc(&p->pd_out[i], ob);
-			if (e == cudaSuccess && hp.log_rate) e = cudaMalloc(&p->pd_in[i], ib);
+			cudaError_t e = p->pd_out[i] ? cudaSuccess : cudaMalloc(&p->pd_out[i], ob);
+			if (e == cudaSuccess && hp.log_rate && !p->pd_in[i]) e = cudaMalloc(&p->pd_in[i], ib);
 			if (e != cudaSuccess) return e == cudaErrorMemoryAllocation ? (cudaGetLastError(), B2NTT_ENOMEM) : cuda_fail(e, "cudaMalloc");
-			CU(cudaEventCreateWithFlags(&p->ev_in[i], cudaEventDisableTiming));
-			CU(cudaEventCreateWithFlags(&p->ev_cmp[i], cudaEventDisableTiming));
-			CU(cudaEventCreateWithFlags(&p->ev_out[i], cudaEventDisableTiming));
+			if (!p->ev_in[i]) CU(cudaEventCreateWithFlags(&p->ev_in[i], cudaEventDisableTiming));
+			if (!p->ev_cmp[i]) CU(cudaEventCreateWithFlags(&p->ev_cmp[i], cudaEventDisableTiming));
+			if (!p->ev_out[i]) CU(cudaEventCreateWithFlags(&p->ev_out[i], cudaEventDisableTiming));
 		}
 		p->pipe_ready = true;
 	}
-	for (int i = 0; i < count; i++) {
+	int rc = B2NTT_OK;
+	cudaError_t ce = cudaSuccess;
+#define PIPE(call)                                      \
+	if (rc == B2NTT_OK && (ce = (call)) != cudaSuccess) rc = cuda_fail(ce, #call)
+	for (int i = 0; i < count && rc == B2NTT_OK; i++) {
 		const int b = i % K;
 		uint32_t* din = hp.log_rate ? p->pd_in[b] : p->pd_out[b];
-		if (i >= K) CU(cudaStreamWaitEvent(p->ps[0], p->ev_out[b], 0));  // the buffer set is free again
-		CU(cudaMemcpyAsync(din, h_in[i], ib, cudaMemcpyHostToDevice, p->ps[0]));
-		CU(cudaEventRecord(p->ev_in[b], p->ps[0]));
-		CU(cudaStreamWaitEvent(p->ps[1], p->ev_in[b], 0));
-		const int rc = run(p, din, p->pd_out[b], false, 0, p->ps[1]);
-		if (rc) return rc;
-		CU(cudaEventRecord(p->ev_cmp[b], p->ps[1]));
-		CU(cudaStreamWaitEvent(p->ps[2], p->ev_cmp[b], 0));
-		CU(cudaMemcpyAsync(h_out[i], p->pd_out[b], ob, cudaMemcpyDeviceToHost, p->ps[2]));
-		CU(cudaEventRecord(p->ev_out[b], p->ps[2]));
+		if (i >= K) PIPE(cudaStreamWaitEvent(p->ps[0], p->ev_out[b], 0));  // the buffer set is free again
+		PIPE(cudaMemcpyAsync(din, h_in[i], ib, cudaMemcpyHostToDevice, p->ps[0]));
+		PIPE(cudaEventRecord(p->ev_in[b], p->ps[0]));
+		PIPE(cudaStreamWaitEvent(p->ps[1], p->ev_in[b], 0));
+		if (rc == B2NTT_OK) rc = run(p, din, p->pd_out[b], false, 0, p->ps[1]);
+		PIPE(cudaEventRecord(p->ev_cmp[b], p->ps[1]));
+		PIPE(cudaStreamWaitEvent(p->ps[2], p->ev_cmp[b], 0));
+		PIPE(cudaMemcpyAsync(h_out[i], p->pd_out[b], ob, cudaMemcpyDeviceToHost, p->ps[2]));
+		PIPE(cudaEventRecord(p->ev_out[b], p->ps[2]));
 	}
-	CU(cudaStreamSynchronize(p->ps[2]));
-	CU(cudaStreamSynchronize(p->ps[0]));
-	return B2NTT_OK;
+#undef PIPE
+	// drain all three streams whatever happened: no copy on the caller's buffers is in flight after the call returns
+	for (int i = 2; i >= 0; i--) {
+		const cudaError_t e = cudaStreamSynchronize(p->ps[i]);
+		if (e != cudaSuccess && rc == B2NTT_OK) rc = cuda_fail(e, "cudaStreamSynchronize");
+	}
+	return rc;
 }
 
 extern "C" int b2ntt_plan_launches(const b2ntt_plan* p) {
@@ -357,6 +373,7 @@ extern "C" const char* b2ntt_strerror(int code) {
 		case B2NTT_ENOMEM: return "out of memory";
 		case B2NTT_ECUDA: return "CUDA error or no usable device";
 		case B2NTT_EUNSUPPORTED: return "not supported by this build";
+		case B2NTT_ECHECK: return "self-check failed";
 		default: return "unknown error";
 	}
 }

@@ -36,7 +36,8 @@ enum {
 	B2NTT_EINVAL = -1,       /* bad argument (what makes AdditiveNTT::apply return false / ASSERT fire) */
 	B2NTT_ENOMEM = -2,       /* host or device allocation failed */
 	B2NTT_ECUDA = -3,        /* CUDA runtime error or no usable device */
-	B2NTT_EUNSUPPORTED = -4  /* valid request this build does not implement */
+	B2NTT_EUNSUPPORTED = -4, /* valid request this build does not implement */
+	B2NTT_ECHECK = -5        /* a requested self-check failed (b2ntt_sumcheck_set_recompute) */
 };
 
 enum { B2NTT_LAYOUT_COMPACT = 0, B2NTT_LAYOUT_BITSLICED = 1 };
@@ -147,6 +148,11 @@ int b2ntt_sumcheck_load_device(b2ntt_sumcheck* sc, void* d_evals, int transposed
 int b2ntt_sumcheck_round_messages(b2ntt_sumcheck* sc, uint32_t* sum, uint32_t* points);
 /* move_to_next_round (sumcheck.cuh:248-299): binds the top remaining variable to challenge[4]. */
 int b2ntt_sumcheck_next_round(b2ntt_sumcheck* sc, const uint32_t* challenge);
+/* From the second round on p(1) is normally DERIVED (p(1) = q(r) + p(0), q = the previous round polynomial, r = the last
+ * challenge) instead of recomputed from the data.  on != 0: every device round computes p(1) from the data as the reference
+ * does (compute_compositions, sumcheck/core/kernels.cuh:5-102) and round_messages returns B2NTT_ECHECK if it differs from
+ * the derived value -- the check a caller (or a test) switches on to make the per-round identities non-tautological. */
+int b2ntt_sumcheck_set_recompute(b2ntt_sumcheck* sc, int on);
 int b2ntt_sumcheck_round(const b2ntt_sumcheck* sc);
 long long b2ntt_sumcheck_launches(const b2ntt_sumcheck* sc);
 

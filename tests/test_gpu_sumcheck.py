@@ -60,6 +60,34 @@ def test_reference_sizes_verifier_consistency(b2, oracle, cuda, num_vars, comp):
     sc.close()
 
 
+@pytest.mark.parametrize("num_vars,comp", [(24, 2), (24, 3), (28, 2)])
+def test_device_p1_equals_the_derived_value_every_round(b2, oracle, cuda, num_vars, comp):
+    """with p(1) derived from the previous round the per-round checks are tautological.  set_recompute makes every
+    device round compute p(1) from the data (as compute_compositions does) and fail with B2NTT_ECHECK on any difference; the
+    messages must also equal those of the default (derived) run word for word.  28 variables = the reference's largest
+    instantiation (sumcheck.cuh:12)."""
+    import torch
+
+    g = torch.Generator(device=cuda).manual_seed(7 * num_vars + comp)
+    d = torch.randint(-2**31, 2**31 - 1, (4 * comp << num_vars,), dtype=torch.int32, device=cuda, generator=g)
+    runs = []
+    for recompute in (True, False):
+        sc = b2.Sumcheck(d.clone(), num_vars, comp, data_is_transposed=False)
+        if recompute:
+            sc.set_recompute(True)
+        rng = np.random.default_rng(num_vars)
+        msgs = []
+        for _ in range(num_vars):
+            s_, p_ = sc.this_round_messages()  # raises B2NTTError(B2NTT_ECHECK) on a mismatch
+            msgs.append((s_.copy(), p_.copy()))
+            sc.move_to_next_round(rng.integers(0, 2**32, 4, dtype=np.uint32))
+        msgs.append(tuple(x.copy() for x in sc.this_round_messages()))
+        runs.append(msgs)
+        sc.close()
+    for (s0, p0), (s1, p1) in zip(*runs):
+        assert np.array_equal(s0, s1) and np.array_equal(p0, p1)
+
+
 def test_sumcheck_argument_errors(b2, cuda):
     with pytest.raises(b2.B2NTTError):
         b2.Sumcheck(np.zeros(4 * 2 << 4, dtype=np.uint32), 4, 2)
