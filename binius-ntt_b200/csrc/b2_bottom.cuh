@@ -30,21 +30,23 @@ struct BottomSmem {
 	uint32_t* IH;   // [8] in-line twiddle, per tile and coset: by stage
 	uint32_t* IL;   // [n_inline][512] in-line twiddle by local line
 	uint32_t* LT;   // [5][32] lane_tw copy
+	Coef4* rows;    // [4][16] the GF(16) coefficient rows of butterfly_lane (b2_constmat.cuh)
 };
 // One CTA runs kBottomTeams teams of 4 warps, each on its own tile.  Warps w and w + 4 share an SM sub-partition and
 // meet at the same CTA barriers, so they execute the same stretch of straight-line butterfly code at the same time:
 // the instruction cache serves both (two independent CTAs per SM ran out of phase and stalled on instruction fetch).
-// layout: [consts 1024][TL 512][IL 5*512][LT 160]  then per team  [coefficient rows 15*108*4][tw 16][TH 8][IH 8][slots 16*32*36]
+// layout: [consts 1024][TL 512][IL 5*512][LT 160][rows 256]  then per team  [coefficient rows 15*108*4][tw 16][TH 8][IH 8][slots 16*32*36]
 constexpr int kBottomTeams = 2;
 B2_HD size_t bottom_team_words() { return (size_t)kUpperMaxTw * kLeafPitch + 16 + 8 + 8 + (size_t)16 * 32 * kUSlotWords; }
-B2_HD size_t bottom_smem_words() { return 1024 + 512 + 5 * 512 + 160 + kBottomTeams * bottom_team_words(); }
+B2_HD size_t bottom_smem_words() { return 1024 + 512 + 5 * 512 + 160 + 256 + kBottomTeams * bottom_team_words(); }
 B2_HD BottomSmem bottom_smem_view(uint32_t* base, int team = 0) {
 	BottomSmem b;
 	b.us.consts = base;
 	b.TL = base + 1024;
 	b.IL = b.TL + 512;
 	b.LT = b.IL + 5 * 512;
-	uint32_t* t = b.LT + 160 + (size_t)team * bottom_team_words();
+	b.rows = reinterpret_cast<Coef4*>(b.LT + 160);  // 16-byte aligned: 1024 + 512 + 2560 + 160 words before it
+	uint32_t* t = b.LT + 160 + 256 + (size_t)team * bottom_team_words();
 	b.us.leaves = reinterpret_cast<Coef4*>(t);
 	b.us.tw = t + kUpperMaxTw * kLeafPitch;
 	b.TH = b.us.tw + 16;
@@ -64,6 +66,7 @@ B2_HD int bottom_stage(const BottomParams& B, int bit) { return B.n_inline + bit
 // once per CTA: tile-independent tables
 B2_HD void bottom_prologue(const BottomParams& B, BottomSmem& bs, int tid, int nthreads, const uint32_t* consts) {
 	for (int i = tid; i < 160; i += nthreads) bs.LT[i] = B.lane_tw[i];
+	for (int i = tid; i < 64; i += nthreads) bs.rows[i] = lane_row_entry(i);
 	for (int idx = tid; idx < 512; idx += nthreads) {
 		if (idx == 0) {
 			bs.TL[0] = 0;
@@ -126,7 +129,12 @@ B2_HD void bottom_phase_b(const BottomParams& B, const BottomSmem& bs, int warp,
 				in_line_dispatch<true>(B.cls[s], U, V, s + B.lane_shift, bs.LT + s * 32, bs.IH[s] ^ bs.IL[s * 512 + l_u], bs.IH[s] ^ bs.IL[s * 512 + l_v]);
 		}
 		const uint32_t w = bs.TH[b] ^ bs.TL[(1 << (8 - b)) + (l_u >> (b + 1))];
-		uniform_dispatch<INV>(B.cls[bottom_stage(B, b)], U, V, w);
+		// twiddles differ per lane: class 5 through the static GF(16) row table (IMAD + LOP3), smaller classes two-sided
+		const int cls = B.cls[bottom_stage(B, b)];
+		if (cls == 5)
+			butterfly_lane<INV>(U, V, w, bs.rows);
+		else
+			uniform_dispatch<INV>(cls, U, V, w);
 		if (!INV && n == nline - 1) {  // last touch: the in-line layers downwards, then the compact image
 #pragma unroll 1
 			for (int s = L0 - 1; s >= 0; s--)

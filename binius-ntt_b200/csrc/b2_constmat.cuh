@@ -130,6 +130,84 @@ B2_HD void butterfly_mat(uint32_t* U, uint32_t* V, const Coef4* c) {
 		for (int i = 0; i < 32; i++) V[i] ^= U[i];
 	}
 }
+// ---- the same product for a twiddle that is private to the THREAD (the per-lane layers of the tile pass) -------------------------
+// A per-thread table of 108 coefficient rows would cost more to build than the product.  Instead the thread computes the 27
+// GF(16) leaf values of its twiddle (packed arithmetic on the 32-bit scalar: about 70 integer operations) and fetches row i of
+// leaf g from a STATIC table of the 16 possible 4 x 4 matrices, rows[i * 16 + lambda] (1 KB of shared memory, filled once per
+// CTA): the 32 lanes of a warp read at most 16 different 16-byte chunks inside one 256-byte span per instruction.
+struct LaneTwiddle {
+	uint32_t y[9];       // y[3 * d3 + d4]: bits 0..3 / 16..19 = the value for d5 = 0 / 1 (d = 0: low half, 1: high half, 2: their sum)
+	const Coef4* rows;   // [4][16]
+	B2_HD explicit LaneTwiddle(uint32_t w, const Coef4* table) : rows(table) {
+		const uint32_t x0 = w & 0x0f0f0f0fu, x1 = (w >> 4) & 0x0f0f0f0fu, x[3] = {x0, x1, x0 ^ x1};  // by nibble parity (d3)
+#pragma unroll
+		for (int d3 = 0; d3 < 3; d3++) {
+			const uint32_t lo = x[d3] & 0x00ff00ffu, hi = (x[d3] >> 8) & 0x00ff00ffu;  // by byte parity (d4)
+			y[3 * d3] = lo, y[3 * d3 + 1] = hi, y[3 * d3 + 2] = lo ^ hi;
+		}
+	}
+	template <int G>
+	B2_HD const Coef4* leaf() const {  // rows of leaf G = 9 d5 + 3 d4 + d3 (the order of coef_leaf_value)
+		constexpr int d5 = G / 9, d4 = (G / 3) % 3, d3 = G % 3;
+		const uint32_t v = y[3 * d3 + d4];
+		const uint32_t lam = d5 == 0 ? (v & 15u) : d5 == 1 ? (v >> 16) : ((v ^ (v >> 16)) & 15u);
+		return rows + lam;
+	}
+};
+template <int H, int G0>
+struct LaneMul {
+	static constexpr int N = 1 << H, M = N / 2;
+	static constexpr int L = MatMul<H - 1>::L;
+	static B2_HD void mul(const uint32_t* a, const LaneTwiddle& tw, uint32_t* out) {
+		uint32_t sa[M], z0[M], z2[M], zz[M], za[M];
+#pragma unroll
+		for (int i = 0; i < M; i++) sa[i] = a[i] ^ a[M + i];
+		LaneMul<H - 1, G0>::mul(a, tw, z0);
+		LaneMul<H - 1, G0 + L>::mul(a + M, tw, z2);
+		LaneMul<H - 1, G0 + 2 * L>::mul(sa, tw, zz);
+		Sliced<H - 1>::mul_alpha(z2, za);
+#pragma unroll
+		for (int i = 0; i < M; i++) {
+			const uint32_t lo = z0[i] ^ z2[i];
+			out[i] = lo;
+			out[M + i] = zz[i] ^ lo ^ za[i];
+		}
+	}
+};
+template <int G0>
+struct LaneMul<2, G0> {
+	static B2_HD void mul(const uint32_t* a, const LaneTwiddle& tw, uint32_t* out) {
+		const Coef4* c = tw.template leaf<G0>();
+#pragma unroll
+		for (int i = 0; i < 4; i++) {
+			const Coef4 q = c[16 * i];
+			out[i] = sel01(a[0], q.x) ^ sel01(a[1], q.y) ^ sel01(a[2], q.z) ^ sel01(a[3], q.w);
+		}
+	}
+};
+// row table of LaneTwiddle: entry i * 16 + lam = row i of "multiply by lam" (all four terms as 0 / 1 coefficients)
+B2_HD Coef4 lane_row_entry(int idx) { return coef_row<4>((uint32_t)idx & 15u, idx >> 4); }
+
+// U ^= w * V ; V ^= U (forward) or V ^= U ; U ^= w * V (inverse) for a thread-private w in GF(2^32)
+template <bool INV>
+B2_HD void butterfly_lane(uint32_t* U, uint32_t* V, uint32_t w, const Coef4* rows) {
+	if (INV) {
+#pragma unroll
+		for (int i = 0; i < 32; i++) V[i] ^= U[i];
+	}
+	{
+		const LaneTwiddle tw(w, rows);
+		uint32_t p[32];
+		LaneMul<5, 0>::mul(V, tw, p);
+#pragma unroll
+		for (int i = 0; i < 32; i++) U[i] ^= p[i];
+	}
+	if (!INV) {
+#pragma unroll
+		for (int i = 0; i < 32; i++) V[i] ^= U[i];
+	}
+}
+
 template <bool INV>
 B2_HD void butterfly_mat_dispatch(int cls, uint32_t* U, uint32_t* V, const Coef4* c) {
 	switch (cls) {
