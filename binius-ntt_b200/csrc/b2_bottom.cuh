@@ -46,6 +46,7 @@ B2_HD BottomSmem bottom_smem_view(uint32_t* base, int team = 0) {
 	b.IL = b.TL + 512;
 	b.LT = b.IL + 5 * 512;
 	b.rows = reinterpret_cast<Coef4*>(b.LT + 160);  // 16-byte aligned: 1024 + 512 + 2560 + 160 words before it
+	b.us.rows16 = b.rows;                           // the same table serves the coefficient-table build of phase A
 	uint32_t* t = b.LT + 160 + 256 + (size_t)team * bottom_team_words();
 	b.us.leaves = reinterpret_cast<Coef4*>(t);
 	b.us.tw = t + kUpperMaxTw * kLeafPitch;

@@ -18,6 +18,7 @@ __global__ void __launch_bounds__(kUpperWarps * 32, 2) upper_kernel(const __grid
 	UpperSmem sm = upper_smem_view(usmem_raw);
 	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 	for (int i = threadIdx.x; i < 1024; i += kUpperWarps * 32) sm.consts[i] = P.consts[i];
+	upper_rows16_fill(sm, (int)threadIdx.x, kUpperWarps * 32);
 	__syncthreads();
 	if (P.k >= 4) {
 		// The CTA works on one group of 2^k super-lines (512 lines) at a time, k / 2 layer pairs with a CTA barrier between

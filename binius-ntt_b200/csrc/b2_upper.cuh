@@ -145,20 +145,22 @@ struct UpperParams {
 constexpr int kUSlotWords = 36;  // padded line slot in the exchange buffer (as b2_pass.cuh)
 B2_HD size_t upper_smem_words(int k) {
 	(void)k;
-	return (size_t)kLeafTableWords + 64 + 1024 + (size_t)512 * kUSlotWords;
+	return (size_t)kLeafTableWords + 64 + 1024 + 256 + (size_t)512 * kUSlotWords;
 }
 struct UpperSmem {
 	Coef4* leaves;     // [2^k - 1][lpitch] coefficient rows (b2_constmat.cuh)
 	uint32_t* tw;      // [64] twiddle words
 	uint32_t* consts;  // [32][32] copy of the subspace constants
 	uint32_t* slots;   // [512 lines][kUSlotWords]: super-line x, line l at (x << ls) + l; k = 2: 4 super-lines per warp
+	const Coef4* rows16;  // [4][16] static: row i of the GF(16) matrix of lam at i * 16 + lam (lane_row_entry), filled once per CTA
 };
 B2_HD UpperSmem upper_smem_view(uint32_t* base) {
 	UpperSmem sm;
 	sm.leaves = reinterpret_cast<Coef4*>(base);
 	sm.tw = base + kLeafTableWords;
 	sm.consts = sm.tw + 64;
-	sm.slots = sm.consts + 1024;
+	sm.rows16 = reinterpret_cast<const Coef4*>(sm.consts + 1024);
+	sm.slots = sm.consts + 1024 + 256;
 	return sm;
 }
 
@@ -180,6 +182,12 @@ B2_HD uint64_t upper_line(const UpperParams& P, const UGroup& c, int x, int lane
 }
 // table index of the twiddle of layer i for the super-line x (depends on x >> (i+1))
 B2_HD int upper_tw_index(int k, int i, int x) { return (1 << (k - 1 - i)) - 1 + (x >> (i + 1)); }
+
+// once per CTA, before the first upper_leaves
+B2_HD void upper_rows16_fill(const UpperSmem& sm, int tid, int nthreads) {
+	Coef4* t = const_cast<Coef4*>(sm.rows16);
+	for (int i = tid; i < 64; i += nthreads) t[i] = lane_row_entry(i);
+}
 
 // twiddle words of (row, hi): threads tid < 2^k - 1; consts = the [32][32] constants (a shared-memory copy on the GPU)
 B2_HD void upper_twiddles(const UpperParams& P, UpperSmem& sm, const UGroup& c, int tid, const uint32_t* consts) {
@@ -204,7 +212,8 @@ B2_HD void upper_leaves(const UpperParams& P, UpperSmem& sm, int tid, int nthrea
 		int lg = 0;
 		while ((tw + 1) >> (lg + 1)) lg++;
 		const int hw = P.cls[P.k - 1 - lg];
-		if ((r >> 2) < coef_leaves(hw)) sm.leaves[tw * lp + r] = coef_row(coef_leaf_value(sm.tw[tw], hw, r >> 2), r & 3);
+		// a row of a twiddle's table is a row of one of the 16 GF(16) matrices: copied from the static table
+		if ((r >> 2) < coef_leaves(hw)) sm.leaves[tw * lp + r] = sm.rows16[(r & 3) * 16 + coef_leaf_value(sm.tw[tw], hw, r >> 2)];
 	}
 }
 

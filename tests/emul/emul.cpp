@@ -35,6 +35,7 @@ static void run_upper(const UpperParams& P) {
 	std::vector<uint32_t> mem(upper_smem_words(4) + 8);
 	UpperSmem sm = upper_smem_view(mem.data());
 	const int T = kUpperWarps * 32;
+	for (int t = 0; t < T; t++) upper_rows16_fill(sm, t, T);
 	for (uint64_t grp = 0; grp < P.n_groups; grp++) {
 		const UGroup c = upper_group(P, grp);
 		for (int t = 0; t < T; t++) upper_twiddles(P, sm, c, t, P.consts);
