@@ -171,7 +171,7 @@ class Plan:
         kind = (C.c_int * 16)()
         n = lib().b2ntt_exec_profile(self._h, d_in.data_ptr(), d_out.data_ptr(), _stream_ptr(stream), ms, kind, 16)
         _check(min(n, 0), "b2ntt_exec_profile")
-        return [(("b2::pass_kernel", "b2::upper_kernel", "b2::bottom_kernel")[kind[i]], float(ms[i])) for i in range(n)]
+        return [(("b2::pass_kernel", "b2::upper_kernel", "b2::bottom_kernel", "b2::upper_kernel", "b2::bsl_kernel")[kind[i]], float(ms[i])) for i in range(n)]
 
     def exec_inverse(self, d_in, d_out=None, coset=0, stream=None):
         self._dev_ok(d_in, self.in_words, "d_in")

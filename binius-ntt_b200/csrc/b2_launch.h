@@ -9,6 +9,7 @@ namespace b2 {
 struct PassParams;
 struct UpperParams;
 struct BottomParams;
+struct BslParams;
 
 // element-wise path for transforms with fewer than two 128-byte lines per row
 struct TinyParams {
@@ -26,6 +27,7 @@ struct TinyParams {
 int launch_pass(const PassParams& P, cudaStream_t stream);
 int launch_upper(const UpperParams& U, cudaStream_t stream);  // b2_upper.cu
 int launch_bottom(const BottomParams& B, cudaStream_t stream);  // b2_bottom.cu
+int launch_bsl(const BslParams& L, cudaStream_t stream);        // b2_bsl.cu
 int launch_tiny_fanout(const TinyParams& T, cudaStream_t stream);
 int launch_tiny_layers(const TinyParams& T, cudaStream_t stream);
 

@@ -13,6 +13,7 @@
 
 #include "b2_pass.cuh"
 #include "b2_bottom.cuh"
+#include "b2_bsl.cuh"
 
 namespace b2 {
 
@@ -21,7 +22,7 @@ struct PassDesc {
 	int k;        // line bits fused
 	int in_line;  // run the in-line layers in this pass
 	int kind;     // 0: bundle pass through shared memory (b2_pass.cuh), 1: upper pass with warp-uniform twiddles (b2_upper.cuh),
-	              // 2: lowest pass on 512-line tiles (b2_bottom.cuh)
+	              // 2: lowest pass on 512-line tiles (b2_bottom.cuh), 4: block-sliced lowest pass on 32-block tiles (b2_bsl.cuh)
 };
 
 struct HostPlan {
@@ -115,10 +116,13 @@ inline int plan_build(HostPlan& hp, int field_bits, int layout, int log_h, int l
 	hp.tiny = nbf < 1;
 	const bool use_upper6 = use_upper != 3;  // 3: as 2 but without the 6-bit passes (A/B runs)
 	if (use_upper == 3) use_upper = 2;
+	// 5: as 2 with the block-sliced lowest pass (compact images with at least 2^15 words per row); it owns 5 line bits
+	const bool bsl = use_upper == 5 && !hp.sliced_io && hp.nb >= 10;
+	if (use_upper == 5) use_upper = 2;
 	if (!hp.tiny && use_upper == 2 && nbf >= 9 - hp.batch_bits) {
+		const int kb = bsl ? 5 : 9 - hp.batch_bits;
 		// lowest pass: 512-line tiles (kind 2) = 9 - batch_bits butterfly line bits; above it upper passes of 4
 		// (or 2) line bits; an odd remainder goes to one bundle pass of 3 (or 1) bits at the top
-		const int kb = 9 - hp.batch_bits;
 		int left = nbf - kb, q = hp.batch_bits + nbf;
 		if (left & 1) {
 			const int kt = left >= 3 ? 3 : 1;
@@ -144,7 +148,7 @@ inline int plan_build(HostPlan& hp, int field_bits, int layout, int log_h, int l
 			q -= 4, left -= 4;
 			hp.passes.push_back(PassDesc{q, 4, 0, 1});
 		}
-		hp.passes.push_back(PassDesc{hp.batch_bits, kb, 1, 2});
+		hp.passes.push_back(PassDesc{hp.batch_bits, kb, 1, bsl ? 4 : 2});
 	} else if (!hp.tiny && use_upper && nbf > max_bits && max_bits >= 6) {
 		// lowest pass: the bundle pass with the in-line layers (8 or 9 line bits); everything above it
 		// has strides >= 32 lines and runs as upper passes of 4 (or 2) line bits, highest first
@@ -180,6 +184,16 @@ inline int plan_build(HostPlan& hp, int field_bits, int layout, int log_h, int l
 	return 0;
 }
 
+// the block-sliced pass reads and writes COMPACT lines: the pass executed before it stores compact, the one after it loads compact
+inline bool plan_next_is_bsl(const HostPlan& hp, int n, bool inverse) {
+	const int np = (int)hp.passes.size();
+	return n + 1 < np && (inverse ? hp.passes[np - 2 - n] : hp.passes[n + 1]).kind == 4;
+}
+inline bool plan_prev_is_bsl(const HostPlan& hp, int n, bool inverse) {
+	const int np = (int)hp.passes.size();
+	return n >= 1 && (inverse ? hp.passes[np - n] : hp.passes[n - 1]).kind == 4;
+}
+
 // Parameters of the n-th pass in EXECUTION order (forward: highest line bits first; inverse: the
 // reverse).  consts / lane_tw point to wherever the kernels will read the tables (device memory on
 // the GPU, hp's own arrays in the CPU emulation).  Intermediate passes leave the lines bit-sliced.
@@ -202,8 +216,8 @@ inline void plan_fill_pass(const HostPlan& hp, PassParams& P, int n, const uint3
 	P.lane_tw = lane_tw;
 	P.log_h = hp.log_h, P.log_rate = hp.log_rate, P.limbs_log = hp.limbs_log;
 	P.n_inline = hp.n_inline, P.lane_shift = hp.lane_shift, P.batch_bits = hp.batch_bits;
-	P.src_sliced = (hp.sliced_io || !first_pass) ? 1 : 0;
-	P.dst_sliced = (hp.sliced_io || !last_pass) ? 1 : 0;
+	P.src_sliced = (hp.sliced_io || (!first_pass && !plan_prev_is_bsl(hp, n, inverse))) ? 1 : 0;
+	P.dst_sliced = (hp.sliced_io || (!last_pass && !plan_next_is_bsl(hp, n, inverse))) ? 1 : 0;
 	P.nb = hp.nb, P.q0 = pd.q0, P.k = pd.k, P.in_line = pd.in_line;
 	P.inverse = inverse ? 1 : 0;
 	P.coset0 = single ? coset : 0;
@@ -237,8 +251,8 @@ inline void plan_fill_upper(const HostPlan& hp, UpperParams& U, int n, const uin
 	U.log_h = hp.log_h, U.nb = hp.nb, U.q0 = pd.q0, U.k = pd.k;
 	U.ls = pd.k == 6 ? 3 : 5;
 	U.stage0 = hp.n_inline + pd.q0 - hp.batch_bits;
-	U.src_sliced = (hp.sliced_io || !first_pass) ? 1 : 0;
-	U.dst_sliced = (hp.sliced_io || !last_pass) ? 1 : 0;
+	U.src_sliced = (hp.sliced_io || (!first_pass && !plan_prev_is_bsl(hp, n, inverse))) ? 1 : 0;
+	U.dst_sliced = (hp.sliced_io || (!last_pass && !plan_next_is_bsl(hp, n, inverse))) ? 1 : 0;
 	U.inverse = inverse ? 1 : 0;
 	U.n_groups = (uint64_t)rows << (hp.nb - pd.k - U.ls);
 	U.lpitch = kLeafRows4;
@@ -263,6 +277,29 @@ inline void plan_fill_bottom(const HostPlan& hp, BottomParams& B, int n, const u
 	B.lane_tw = lane_tw;
 	B.n_inline = hp.n_inline, B.lane_shift = hp.lane_shift, B.batch_bits = hp.batch_bits;
 	memcpy(B.cls, hp.cls, 32);
+}
+
+// Parameters of the block-sliced lowest pass (kind 4).
+inline void plan_fill_bsl(const HostPlan& hp, BslParams& L, int n, const uint32_t* src, uint32_t* dst, const uint32_t* consts, bool inverse,
+                          int coset, bool one_coset = false) {
+	memset(&L, 0, sizeof L);
+	const int np = (int)hp.passes.size();
+	const uint64_t row_words = (uint64_t)32 << hp.nb;
+	const bool single = inverse || one_coset;
+	const int rows = single ? hp.batch : hp.batch << hp.log_rate;
+	const bool first_pass = n == 0;
+	(void)np;
+	L.src = first_pass ? src : dst;
+	L.dst = dst;
+	L.src_row_words = L.dst_row_words = row_words;
+	L.src_row_shift = (first_pass && !single) ? hp.log_rate : 0;
+	L.coset_mask = single ? 0u : ((1u << hp.log_rate) - 1);
+	L.coset0 = single ? coset : 0;
+	L.consts = consts;
+	L.log_h = hp.log_h, L.limbs_log = hp.limbs_log;
+	L.inverse = inverse ? 1 : 0;
+	L.tiles_per_row_log = hp.nb - 10;
+	L.n_tiles = (uint64_t)rows << L.tiles_per_row_log;
 }
 
 // Top phase of a transform split over 2^log_seg devices: the buffer holds

@@ -70,7 +70,7 @@ extern "C" int b2ntt_plan_create(b2ntt_plan** out, int field_bits, int layout, i
 	const int line_bits = log_h + log_rate + (field_bits == 128 ? 2 : 0) - 5;
 	const uint64_t total_lines = (uint64_t)(batch > 0 ? batch : 1) << (line_bits > 0 ? line_bits : 0);
 	int upper = total_lines >= (uint64_t(1) << 22) ? 2 : 0;
-	if (const char* e = getenv("B2NTT_UPPER")) upper = atoi(e);  // tuning knob: 0 = bundle passes only, 1 = upper passes over a bundle pass, 2 = upper passes over the tile pass
+	if (const char* e = getenv("B2NTT_UPPER")) upper = atoi(e);  // tuning knob: 0 = bundle passes only, 1 = upper passes over a bundle pass, 2 = upper passes over the tile pass, 5 = upper passes over the block-sliced pass
 	if (plan_build(p->hp, field_bits, layout, log_h, log_rate, batch, cta, glines, upper)) {
 		delete p;
 		return B2NTT_EINVAL;
@@ -157,6 +157,10 @@ static int run(b2ntt_plan* p, const void* d_in, void* d_out, bool inverse, int c
 		} else if (kind == 2) {
 			plan_fill_bottom(hp, B, n, src, dst, p->d_consts, p->d_lane_tw, inverse, coset, one_coset);
 			if (launch_bottom(B, st)) return cuda_fail(cudaGetLastError(), "launch_bottom");
+		} else if (kind == 4) {
+			BslParams L;
+			plan_fill_bsl(hp, L, n, src, dst, p->d_consts, inverse, coset, one_coset);
+			if (launch_bsl(L, st)) return cuda_fail(cudaGetLastError(), "launch_bsl");
 		} else {
 			plan_fill_pass(hp, P, n, src, dst, p->d_consts, p->d_lane_tw, inverse, coset, one_coset);
 			if (launch_pass(P, st)) return cuda_fail(cudaGetLastError(), "launch_pass");

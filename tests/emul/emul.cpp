@@ -89,6 +89,29 @@ static void run_bottom(const BottomParams& B) {
 	}
 }
 
+// block-sliced lowest pass (b2_bsl.cuh): the same phase functions as bsl_kernel, one tile at a time
+template <bool INV>
+static void run_bsl(const BslParams& P) {
+	std::vector<uint32_t> mem(bsl_smem_words() + 8);
+	BslSmem sm = bsl_smem_view(mem.data());
+	const int T = kBslThreads, S = bsl_stages(P);
+	for (int i = 0; i < 1024; i++) sm.consts[i] = P.consts[i];
+	for (int t = 0; t < T; t++) bsl_prologue(P, sm, t, T);
+	for (uint64_t tile = 0; tile < P.n_tiles; tile++) {
+		const BslTile bt = bsl_tile_of(P, tile);
+		for (int t = 0; t < T; t++) bsl_copy<false>(P, sm, bt, t), bsl_tile_twiddles(P, sm, bt, t);
+		for (int t = 0; t < T; t++) bsl_transpose(sm, t);
+		for (int step = 0; step < S; step++) {
+			const int s = INV ? step : S - 1 - step;
+			if (bsl_has_table(P, s))
+				for (int t = 0; t < T; t++) bsl_build_tables(P, sm, s, t);
+			for (int t = 0; t < T; t++) bsl_stage<INV>(P, sm, s, t);
+		}
+		for (int t = 0; t < T; t++) bsl_transpose(sm, t);
+		for (int t = 0; t < T; t++) bsl_copy<true>(P, sm, bt, t);
+	}
+}
+
 extern "C" int emul_antt_sched(int field_bits, int layout, int log_h, int log_rate, int batch, const uint32_t* in,
                                uint32_t* out, int inverse, int coset, int cta_threads, int group_lines, int use_upper) {
 	HostPlan hp;
@@ -108,6 +131,12 @@ extern "C" int emul_antt_sched(int field_bits, int layout, int log_h, int log_ra
 		if (kind == 1) {
 			plan_fill_upper(hp, U, n, in, out, hp.consts, inverse != 0, coset);
 			if (inverse) run_upper<true>(U); else run_upper<false>(U);
+			continue;
+		}
+		if (kind == 4) {
+			BslParams L;
+			plan_fill_bsl(hp, L, n, in, out, hp.consts, inverse != 0, coset);
+			if (inverse) run_bsl<true>(L); else run_bsl<false>(L);
 			continue;
 		}
 		plan_fill_pass(hp, P, n, in, out, hp.consts, hp.lane_tw, inverse != 0, coset);

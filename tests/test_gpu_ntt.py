@@ -41,12 +41,12 @@ def test_golden_md5_gf32_large(b2, oracle, cuda, log_rate, log_h):
     plan.close()
 
 
-@pytest.fixture(params=["auto", "tile", "bundle"])
+@pytest.fixture(params=["auto", "tile", "bundle", "bsl"])
 def schedule(request, monkeypatch):
     """the plan picks its pass schedule by size (b2ntt_plan_create); B2NTT_UPPER pins it, so that the upper/tile kernels
     and the bundle-pass kernel each meet every small edge case on the GPU"""
     if request.param != "auto":
-        monkeypatch.setenv("B2NTT_UPPER", {"tile": "2", "bundle": "0"}[request.param])
+        monkeypatch.setenv("B2NTT_UPPER", {"tile": "2", "bundle": "0", "bsl": "5"}[request.param])
     else:
         monkeypatch.delenv("B2NTT_UPPER", raising=False)
     return request.param

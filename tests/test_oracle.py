@@ -171,6 +171,20 @@ def test_emulated_kernels_match_oracle(oracle, emul, field_bits, layout, log_h, 
     assert np.array_equal(back, src)
 
 
+@pytest.mark.parametrize("field_bits,log_h,log_rate", [(128, 13, 0), (128, 14, 1), (128, 16, 0), (32, 15, 0), (32, 16, 2), (32, 18, 0), (128, 17, 0)])
+def test_emulated_block_sliced_pass(oracle, emul, field_bits, log_h, log_rate):
+    """schedule 5: the block-sliced lowest pass (b2_bsl.cuh) under the upper passes, forward and inverse"""
+    limbs = field_bits // 32
+    x = _rand((1 << log_h) * limbs, 41 * log_h + log_rate)
+    out = np.zeros((1 << (log_h + log_rate)) * limbs, dtype=np.uint32)
+    assert emul.emul_antt_sched(field_bits, 0, log_h, log_rate, 1, x, out, 0, 0, 0, 0, 5) == 0
+    assert np.array_equal(out, oracle.antt_forward(x, log_h, log_rate, limbs))
+    n = (1 << log_h) * limbs
+    back = np.zeros(n, dtype=np.uint32)
+    assert emul.emul_antt_sched(field_bits, 0, log_h, log_rate, 1, np.ascontiguousarray(out[:n]), back, 1, 0, 0, 0, 5) == 0
+    assert np.array_equal(back, x)
+
+
 def test_plan_constants_and_products_match_oracle(oracle, emul):
     for log_h, log_rate in [(20, 0), (20, 2), (28, 0), (28, 4)]:
         c = np.zeros(32 * 32, dtype=np.uint32)
