@@ -15,6 +15,9 @@ __global__ void __launch_bounds__(kBottomTeams * 128, 1) bottom_kernel(const __g
 	BottomSmem bs = bottom_smem_view(bsmem_raw, team);
 	const UpperParams& P = B.up;
 	const int nline = 5 - B.batch_bits;
+	// all four phase-A layers of class 5 (the usual case at large log_n): no coefficient table, the butterflies take the
+	// warp-uniform twiddle word through the static GF(16) rows, and the barrier in front of the table build goes away
+	const bool nt = P.cls[0] == 5 && P.cls[1] == 5 && P.cls[2] == 5 && P.cls[3] == 5;
 	for (int i = threadIdx.x; i < 1024; i += kBottomTeams * 128) bs.us.consts[i] = P.consts[i];
 	__syncthreads();
 	bottom_prologue(B, bs, (int)threadIdx.x, kBottomTeams * 128, bs.us.consts);
@@ -32,14 +35,26 @@ __global__ void __launch_bounds__(kBottomTeams * 128, 1) bottom_kernel(const __g
 			upper_twiddles(P, bs.us, c, tid, bs.us.consts);
 			bottom_tile_tables(B, bs, c, tid - 16, bs.us.consts);
 		}
-		__syncthreads();
-		if (active) upper_leaves(P, bs.us, tid, T);
+		if (!nt) {
+			__syncthreads();
+			if (active) upper_leaves(P, bs.us, tid, T);
+		}
 		copy_wait_all();
 		__syncthreads();
 		if (!INV) {
-			if (active) upper_pair<false>(P, bs.us, lane, warp, 2, 0, 3, true, false);
+			if (active) {
+				if (nt)
+					upper_pair<false, true>(P, bs.us, lane, warp, 2, 0, 3, true, false);
+				else
+					upper_pair<false, false>(P, bs.us, lane, warp, 2, 0, 3, true, false);
+			}
 			__syncthreads();
-			if (active) upper_pair<false>(P, bs.us, lane, warp << 2, 0, 0, 1, false, false);
+			if (active) {
+				if (nt)
+					upper_pair<false, true>(P, bs.us, lane, warp << 2, 0, 0, 1, false, false);
+				else
+					upper_pair<false, false>(P, bs.us, lane, warp << 2, 0, 0, 1, false, false);
+			}
 			__syncwarp();
 		}
 		if (active) {
@@ -53,9 +68,19 @@ __global__ void __launch_bounds__(kBottomTeams * 128, 1) bottom_kernel(const __g
 			}
 		}
 		if (INV) {
-			if (active) upper_pair<true>(P, bs.us, lane, warp << 2, 0, 0, 1, false, false);
+			if (active) {
+				if (nt)
+					upper_pair<true, true>(P, bs.us, lane, warp << 2, 0, 0, 1, false, false);
+				else
+					upper_pair<true, false>(P, bs.us, lane, warp << 2, 0, 0, 1, false, false);
+			}
 			__syncthreads();
-			if (active) upper_pair<true>(P, bs.us, lane, warp, 2, 0, 3, false, true);
+			if (active) {
+				if (nt)
+					upper_pair<true, true>(P, bs.us, lane, warp, 2, 0, 3, false, true);
+				else
+					upper_pair<true, false>(P, bs.us, lane, warp, 2, 0, 3, false, true);
+			}
 		}
 		__syncwarp();
 		if (active) upper_copy<true>(P, bs.us, c, 0, INV ? warp : warp << 2, INV ? 4 : 1, 4, 0, 1, lane);

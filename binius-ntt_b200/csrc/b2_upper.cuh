@@ -244,7 +244,9 @@ B2_HD void line_store(uint32_t* p, const uint32_t* w) {
 // all 4 butterflies, which keeps the executed code inside the instruction cache.
 //   first: the slots hold lines as copied from the pass input (transpose compact lines on first touch)
 //   last : the slots are copied to the pass output afterwards (transpose back for a compact output)
-template <bool INV>
+//   NT   : "no table": every layer is of class 5 and the butterfly takes the twiddle WORD (sm.tw) through the static GF(16)
+//          rows (butterfly_lane), so the caller does not build sm.leaves at all
+template <bool INV, bool NT = false>
 B2_HD void upper_pair(const UpperParams& P, const UpperSmem& sm, int lane, int xbase, int xshift, int slot_off, int b1, bool first, bool last) {
 	const int k = P.k, ls = P.ls, l = lane & ((1 << ls) - 1);  // the lane's line inside every super-line it meets
 #pragma unroll 1
@@ -265,7 +267,10 @@ B2_HD void upper_pair(const UpperParams& P, const UpperSmem& sm, int lane, int x
 				transpose32(U);
 				transpose32(V);
 			}
-			butterfly_mat_dispatch<INV>(cls, U, V, sm.leaves + P.lpitch * upper_tw_index(k, bit, xu));
+			if (NT)
+				butterfly_lane<INV>(U, V, sm.tw[upper_tw_index(k, bit, xu)], sm.rows16);
+			else
+				butterfly_mat_dispatch<INV>(cls, U, V, sm.leaves + P.lpitch * upper_tw_index(k, bit, xu));
 			if (last && step == 1 && !P.dst_sliced) {
 				transpose32(U);
 				transpose32(V);

@@ -73,17 +73,32 @@ static void run_bottom(const BottomParams& B) {
 		const UGroup c = upper_group(P, grp);
 		for (int t = 0; t < T; t++) upper_twiddles(P, bs.us, c, t, P.consts), bottom_tile_tables(B, bs, c, t - 16, P.consts);
 		for (int lane = 0; lane < 32; lane++) upper_copy<false>(P, bs.us, c, 0, 0, 1, 16, 0, 1, lane);
-		for (int t = 0; t < T; t++) upper_leaves(P, bs.us, t, T);
+		// as bottom_kernel: no coefficient table when the four phase-A layers are all of class 5
+		const bool nt = P.cls[0] == 5 && P.cls[1] == 5 && P.cls[2] == 5 && P.cls[3] == 5;
+		if (!nt)
+			for (int t = 0; t < T; t++) upper_leaves(P, bs.us, t, T);
 		if (!INV) {
-			for (int t = 0; t < T; t++) upper_pair<false>(P, bs.us, t & 31, t >> 5, 2, 0, 3, true, false);
-			for (int t = 0; t < T; t++) upper_pair<false>(P, bs.us, t & 31, (t >> 5) << 2, 0, 0, 1, false, false);
+			for (int t = 0; t < T; t++) {
+				if (nt) upper_pair<false, true>(P, bs.us, t & 31, t >> 5, 2, 0, 3, true, false);
+				else upper_pair<false, false>(P, bs.us, t & 31, t >> 5, 2, 0, 3, true, false);
+			}
+			for (int t = 0; t < T; t++) {
+				if (nt) upper_pair<false, true>(P, bs.us, t & 31, (t >> 5) << 2, 0, 0, 1, false, false);
+				else upper_pair<false, false>(P, bs.us, t & 31, (t >> 5) << 2, 0, 0, 1, false, false);
+			}
 		}
 		for (int iter = 0; iter < 2; iter++)
 			for (int n = 0; n < nline; n++)
 				for (int t = 0; t < T; t++) bottom_phase_b<INV>(B, bs, t >> 5, t & 31, iter, n);
 		if (INV) {
-			for (int t = 0; t < T; t++) upper_pair<true>(P, bs.us, t & 31, (t >> 5) << 2, 0, 0, 1, false, false);
-			for (int t = 0; t < T; t++) upper_pair<true>(P, bs.us, t & 31, t >> 5, 2, 0, 3, false, true);
+			for (int t = 0; t < T; t++) {
+				if (nt) upper_pair<true, true>(P, bs.us, t & 31, (t >> 5) << 2, 0, 0, 1, false, false);
+				else upper_pair<true, false>(P, bs.us, t & 31, (t >> 5) << 2, 0, 0, 1, false, false);
+			}
+			for (int t = 0; t < T; t++) {
+				if (nt) upper_pair<true, true>(P, bs.us, t & 31, t >> 5, 2, 0, 3, false, true);
+				else upper_pair<true, false>(P, bs.us, t & 31, t >> 5, 2, 0, 3, false, true);
+			}
 		}
 		for (int lane = 0; lane < 32; lane++) upper_copy<true>(P, bs.us, c, 0, 0, 1, 16, 0, 1, lane);
 	}
