@@ -58,6 +58,7 @@ def lib():
         L.b2ntt_sumcheck_round.argtypes = [vp]
         L.b2ntt_sumcheck_launches.argtypes = [vp]
         L.b2ntt_sumcheck_set_recompute.argtypes = [vp, i]
+        L.b2ntt_sumcheck_round_static.argtypes = [vp, i, i, vp, vp, vp]
         L.b2ntt_general_create.argtypes = [C.POINTER(vp), i, vp, i]
         L.b2ntt_general_destroy.argtypes = [vp]
         L.b2ntt_general_exec.argtypes = [vp, vp, vp, i, vp]

@@ -63,5 +63,7 @@ inline int pointer_device(const void* p) {
 
 // records the CUDA error text for b2ntt_last_cuda_error() and returns B2NTT_ECUDA (b2ntt.cu)
 int report_cuda_error(cudaError_t e, const char* where);
+// records `text` the same way and returns B2NTT_ELIMIT: a size beyond the fixed scratch of a no-allocation entry point (b2ntt.cu)
+int report_limit_error(const char* text);
 
 }  // namespace b2

@@ -20,6 +20,7 @@
 #include <cuda_runtime.h>
 
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <vector>
 
@@ -363,3 +364,84 @@ extern "C" int b2ntt_sumcheck_next_round(b2ntt_sumcheck* s, const uint32_t* chal
 
 extern "C" int b2ntt_sumcheck_round(const b2ntt_sumcheck* s) { return s ? s->round : B2NTT_EINVAL; }
 extern "C" long long b2ntt_sumcheck_launches(const b2ntt_sumcheck* s) { return s ? (long long)s->launches : B2NTT_EINVAL; }
+
+// ================================================================================================================================
+// b2ntt_sumcheck_round_static: the round kernel for callers that cannot allocate (CUDA graph capture, serving loops, harnesses
+// that forbid cudaMalloc).  No counterpart in the reference.
+//
+// The only scratch the round needs is the accumulator that sc_round_kernel XORs its per-CTA partial sums into:
+// (C + 1) x 128 words.  Here it lives in a file-scope __device__ array sized for the largest composition (C = 4, 2560 bytes;
+// every GPU that loads the library holds it until exit).  In HOST code the name `g_round_scratch` is only a stand-in for the
+// symbol, not a device address: the address comes from cudaGetSymbolAddress, once per device with that device current, and
+// is what the kernel receives.  Device code (sc_points_kernel) names the array directly.
+// All calls on one device share the array: it is cleared at the start of every call, and calls that overlap on the GPU
+// (different streams, or graph branches) race on it.
+namespace b2 {
+
+constexpr int kStaticRoundWords = (kScMaxC + 1) * 128;
+static __device__ __align__(256) uint32_t g_round_scratch[kStaticRoundWords];
+
+// compute_sum (sumcheck/core/core.cu:81-95) on the device: limb k of the XOR of the 32 elements of batch t has bit b =
+// parity of word 128 t + 32 k + b.  One warp per (t, k); thread 0 of the block then forms sum = p(0) ^ p(1).
+__global__ void __launch_bounds__(32 * 4 * (kScMaxC + 1)) sc_points_kernel(int C, uint32_t* __restrict__ points, uint32_t* __restrict__ sum) {
+	const int w = threadIdx.x >> 5, b = threadIdx.x & 31;  // w = 4 t + k
+	if (w < 4 * (C + 1)) {
+		const uint32_t limb = __ballot_sync(0xffffffffu, __popc(g_round_scratch[32 * w + b]) & 1);
+		if (b == 0) points[w] = limb;
+	}
+	__syncthreads();
+	if (threadIdx.x < 4) sum[threadIdx.x] = points[threadIdx.x] ^ points[4 + threadIdx.x];
+}
+
+namespace {
+struct StaticRoundDevice {
+	uint32_t* scratch = nullptr;  // device address of g_round_scratch on this device
+	int sms = 0;
+};
+StaticRoundDevice g_static_round[64];
+std::mutex g_static_round_mutex;
+
+// once per device, with that device current
+int static_round_setup(int device, StaticRoundDevice** out) {
+	if (device < 0 || device >= 64) return B2NTT_EINVAL;
+	std::lock_guard<std::mutex> lock(g_static_round_mutex);
+	StaticRoundDevice& d = g_static_round[device];
+	if (!d.scratch) {
+		uint32_t* ptr = nullptr;
+		int sms = 0;
+		SCU(cudaGetSymbolAddress((void**)&ptr, g_round_scratch));
+		SCU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+		SCU(cudaFuncSetAttribute(sc_round_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((kMulSmemWords + kStaticRoundWords) * sizeof(uint32_t))));
+		d.sms = sms, d.scratch = ptr;
+	}
+	*out = &d;
+	return B2NTT_OK;
+}
+}  // namespace
+
+}  // namespace b2
+
+extern "C" int b2ntt_sumcheck_round_static(const void* d_evals, int num_vars, int composition_size, void* d_points, void* d_sum, void* stream) {
+	if (!d_evals || !d_points || !d_sum) return B2NTT_EINVAL;
+	if (composition_size > B2NTT_STATIC_ROUND_MAX_COMPOSITION || num_vars > B2NTT_STATIC_ROUND_MAX_VARS)
+		return report_limit_error("b2ntt_sumcheck_round_static: composition_size > 4 (the static scratch holds (4 + 1) x 128 words) or num_vars > 30");
+	if (composition_size < 2 || num_vars < 6) return B2NTT_EINVAL;  // 32 or fewer evaluations are host work in every entry point
+	const int device = pointer_device(d_evals);
+	if (device < 0 || pointer_device(d_points) != device || pointer_device(d_sum) != device) return B2NTT_EINVAL;
+	DeviceGuard guard(device);
+	SCU(guard.err);
+	StaticRoundDevice* dev = nullptr;
+	if (int rc = static_round_setup(device, &dev)) return rc;
+	const int C = composition_size;
+	const uint64_t n0 = uint64_t(1) << num_vars, half_rows = n0 / 64;
+	cudaStream_t st = (cudaStream_t)stream;
+	SCU(cudaMemsetAsync(dev->scratch, 0, (C + 1) * 128 * sizeof(uint32_t), st));  // the last call's sums are still there
+	uint64_t ctas = (half_rows + 31) / 32;
+	if (ctas > (uint64_t)dev->sms * 2) ctas = (uint64_t)dev->sms * 2;
+	const size_t smem = (kMulSmemWords + (C + 1) * 128) * sizeof(uint32_t);
+	sc_round_kernel<<<(unsigned)ctas, kMulThreads, smem, st>>>((const uint32_t*)d_evals, n0 * 4, half_rows, C, 0, dev->scratch);
+	SCU(cudaGetLastError());
+	sc_points_kernel<<<1, 32 * 4 * (kScMaxC + 1), 0, st>>>(C, (uint32_t*)d_points, (uint32_t*)d_sum);
+	SCU(cudaGetLastError());
+	return B2NTT_OK;
+}

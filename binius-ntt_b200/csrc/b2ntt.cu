@@ -23,6 +23,10 @@ static int cuda_fail(cudaError_t e, const char* where) {
 }
 namespace b2 {
 int report_cuda_error(cudaError_t e, const char* where) { return cuda_fail(e, where); }
+int report_limit_error(const char* text) {
+	snprintf(g_cuda_err, sizeof g_cuda_err, "%s", text);
+	return B2NTT_ELIMIT;
+}
 }  // namespace b2
 #define CU(call)                                              \
 	do {                                                      \
@@ -378,6 +382,7 @@ extern "C" const char* b2ntt_strerror(int code) {
 		case B2NTT_ECUDA: return "CUDA error or no usable device";
 		case B2NTT_EUNSUPPORTED: return "not supported by this build";
 		case B2NTT_ECHECK: return "self-check failed";
+		case B2NTT_ELIMIT: return "size beyond the fixed scratch of a no-allocation entry point";
 		default: return "unknown error";
 	}
 }

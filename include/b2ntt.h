@@ -37,7 +37,8 @@ enum {
 	B2NTT_ENOMEM = -2,       /* host or device allocation failed */
 	B2NTT_ECUDA = -3,        /* CUDA runtime error or no usable device */
 	B2NTT_EUNSUPPORTED = -4, /* valid request this build does not implement */
-	B2NTT_ECHECK = -5        /* a requested self-check failed (b2ntt_sumcheck_set_recompute) */
+	B2NTT_ECHECK = -5,       /* a requested self-check failed (b2ntt_sumcheck_set_recompute) */
+	B2NTT_ELIMIT = -6        /* size beyond the fixed scratch of a no-allocation entry point (b2ntt_sumcheck_round_static) */
 };
 
 enum { B2NTT_LAYOUT_COMPACT = 0, B2NTT_LAYOUT_BITSLICED = 1 };
@@ -155,6 +156,20 @@ int b2ntt_sumcheck_next_round(b2ntt_sumcheck* sc, const uint32_t* challenge);
 int b2ntt_sumcheck_set_recompute(b2ntt_sumcheck* sc, int on);
 int b2ntt_sumcheck_round(const b2ntt_sumcheck* sc);
 long long b2ntt_sumcheck_launches(const b2ntt_sumcheck* sc);
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The messages of the FIRST round --
+ * what b2ntt_sumcheck_round_messages returns right after b2ntt_sumcheck_load_device(.., transposed = 1) -- computed with no
+ * object and no allocation of any kind: the accumulator of the round kernel is a static __device__ array of
+ * (B2NTT_STATIC_ROUND_MAX_COMPOSITION + 1) x 128 words (2560 bytes, held by every GPU that loads the library until exit).
+ *   d_evals : composition_size columns of 2^num_vars GF(2^128) evaluations, bit-sliced, read only (device memory)
+ *   d_points: (composition_size + 1) x 4 words, d_sum: 4 words (device memory of the same GPU); written on `stream`,
+ *             valid once the stream reaches that point -- the call does not synchronise and copies nothing to the host.
+ * num_vars 6..B2NTT_STATIC_ROUND_MAX_VARS, composition_size 2..B2NTT_STATIC_ROUND_MAX_COMPOSITION; beyond the maximum:
+ * B2NTT_ELIMIT, with the reason in b2ntt_last_cuda_error().  All calls on a GPU share the one array (cleared at the start
+ * of each call): calls that overlap on the GPU -- two streams, two graph branches -- race; serialise them. */
+#define B2NTT_STATIC_ROUND_MAX_COMPOSITION 4
+#define B2NTT_STATIC_ROUND_MAX_VARS 30
+int b2ntt_sumcheck_round_static(const void* d_evals, int num_vars, int composition_size, void* d_points, void* d_sum, void* stream);
 
 /* ---- additive NTT over GF(2^128) on a caller-supplied basis (full-width twiddles / general domains) ----
  * Generalises AdditiveNTT<T,P> (ntt/additive_ntt.cuh:176-309), whose basis is fixed to beta_i = 1 << i (:281-283) and whose
