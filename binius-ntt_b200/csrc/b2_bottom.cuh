@@ -31,14 +31,15 @@ struct BottomSmem {
 	uint32_t* IL;   // [n_inline][512] in-line twiddle by local line
 	uint32_t* LT;   // [5][32] lane_tw copy
 	Coef4* rows;    // [4][16] the GF(16) coefficient rows of butterfly_lane (b2_constmat.cuh)
+	uint32_t* CW;   // [5][16] position masks of the GF(16) correction of butterfly_in_line_split; [80 + s] = 1: stage s uses it
 };
 // One CTA runs kBottomTeams teams of 4 warps, each on its own tile.  Warps w and w + 4 share an SM sub-partition and
 // meet at the same CTA barriers, so they execute the same stretch of straight-line butterfly code at the same time:
 // the instruction cache serves both (two independent CTAs per SM ran out of phase and stalled on instruction fetch).
-// layout: [consts 1024][TL 512][IL 5*512][LT 160][rows 256]  then per team  [coefficient rows 15*108*4][tw 16][TH 8][IH 8][slots 16*32*36]
+// layout: [consts 1024][TL 512][IL 5*512][LT 160][rows 256][CW 96]  then per team  [coefficient rows 15*108*4][tw 16][TH 8][IH 8][slots 16*32*36]
 constexpr int kBottomTeams = 2;
 B2_HD size_t bottom_team_words() { return (size_t)kUpperMaxTw * kLeafPitch + 16 + 8 + 8 + (size_t)16 * 32 * kUSlotWords; }
-B2_HD size_t bottom_smem_words() { return 1024 + 512 + 5 * 512 + 160 + 256 + kBottomTeams * bottom_team_words(); }
+B2_HD size_t bottom_smem_words() { return 1024 + 512 + 5 * 512 + 160 + 256 + 96 + kBottomTeams * bottom_team_words(); }
 B2_HD BottomSmem bottom_smem_view(uint32_t* base, int team = 0) {
 	BottomSmem b;
 	b.us.consts = base;
@@ -47,7 +48,8 @@ B2_HD BottomSmem bottom_smem_view(uint32_t* base, int team = 0) {
 	b.LT = b.IL + 5 * 512;
 	b.rows = reinterpret_cast<Coef4*>(b.LT + 160);  // 16-byte aligned: 1024 + 512 + 2560 + 160 words before it
 	b.us.rows16 = b.rows;                           // the same table serves the coefficient-table build of phase A
-	uint32_t* t = b.LT + 160 + 256 + (size_t)team * bottom_team_words();
+	b.CW = b.LT + 160 + 256;
+	uint32_t* t = b.CW + 96 + (size_t)team * bottom_team_words();
 	b.us.leaves = reinterpret_cast<Coef4*>(t);
 	b.us.tw = t + kUpperMaxTw * kLeafPitch;
 	b.TH = b.us.tw + 16;
@@ -64,10 +66,82 @@ B2_HD uint32_t xsel(const uint32_t* table, uint64_t bits) {
 }
 B2_HD int bottom_stage(const BottomParams& B, int bit) { return B.n_inline + bit - B.batch_bits; }
 
+// ---- in-line layer with the twiddle split into a thread-uniform word and a small per-position correction -----------------------
+// butterfly_in_line (b2_bundle.cuh) multiplies by 32 arbitrary twiddle WORDS (the twiddle differs from position to position
+// inside a line), a two-sided product that lives on the ALU pipe alone (1087 LOP3).  But the per-position part is small:
+//     W(pos) = wa ^ D(pos),   D = lane_tw ^ (delta on the positions that hold the second line's lanes),
+// wa = the twiddle of the thread's first line, delta = the (kernel-wide) twiddle difference of the two lines; lane_tw collects
+// constants C[s][j] of the lowest index bits.  For the reference basis these are all below 16 -- elements of GF(16), which act
+// on every 4-plane group of the sliced operand separately -- so
+//     X * W = X * wa  (the thread-uniform two-pipe product, LaneMul)  ^  XOR_k X[4 g + k] & cw[i][k]  (16 LOP3 per group),
+// cw[i][k] = the positions whose D has coefficient (i, k) of its GF(16) matrix set.  The stage falls back to butterfly_in_line
+// when some D(pos) >= 16 or the stage's twiddles are not of class 5.
+B2_HD void in_line_split_tables(const BottomParams& B, BottomSmem& bs, int s, const uint32_t* consts) {
+	const int p = s + B.lane_shift;
+	const uint32_t delta = consts[s * 32 + B.n_inline - 1 - s], hi = ~lane_mask_lo(p);
+	bool small = B.cls[s] == 5 && delta < 16u;
+	uint32_t D[4];
+	for (int r = 0; r < 32; r++) {
+		const uint32_t d = B.lane_tw[s * 32 + r] ^ (bitmask(delta, r) & hi);
+		if (r < 4)
+			D[r] = d;
+		else if (d)
+			small = false;
+	}
+	for (int i = 0; i < 4; i++)
+		for (int k = 0; k < 4; k++) {
+			uint32_t m = 0;
+			for (int r = 0; r < 4; r++)
+				if ((Tower<2>::mul(1u << r, 1u << k) >> i) & 1u) m ^= D[r];
+			bs.CW[s * 16 + 4 * i + k] = m;
+		}
+	bs.CW[80 + s] = small ? 1u : 0u;
+}
+
+template <bool INVERSE>
+B2_HD void butterfly_in_line_split(uint32_t* A, uint32_t* B, int p, const uint32_t* cw, uint32_t wa, const Coef4* rows) {
+	const int sh = 1 << p;
+	const uint32_t mu = lane_mask_lo(p);
+	if (INVERSE) {
+#pragma unroll
+		for (int i = 0; i < 32; i++) {
+			A[i] ^= (A[i] & mu) << sh;
+			B[i] ^= (B[i] & mu) << sh;
+		}
+	}
+	{
+		uint32_t X[32], Pr[32];
+#pragma unroll
+		for (int i = 0; i < 32; i++) X[i] = ((A[i] >> sh) & mu) | (B[i] & ~mu);
+		const LaneTwiddle tw(wa, rows);
+		LaneMul<5, 0>::mul(X, tw, Pr);
+		uint32_t c[16];
+#pragma unroll
+		for (int i = 0; i < 16; i++) c[i] = cw[i];
+#pragma unroll
+		for (int g = 0; g < 8; g++) {
+#pragma unroll
+			for (int i = 0; i < 4; i++) {
+				const uint32_t q = Pr[4 * g + i] ^ (X[4 * g] & c[4 * i]) ^ (X[4 * g + 1] & c[4 * i + 1]) ^ (X[4 * g + 2] & c[4 * i + 2]) ^ (X[4 * g + 3] & c[4 * i + 3]);
+				A[4 * g + i] ^= q & mu;
+				B[4 * g + i] ^= (q >> sh) & mu;
+			}
+		}
+	}
+	if (!INVERSE) {
+#pragma unroll
+		for (int i = 0; i < 32; i++) {
+			A[i] ^= (A[i] & mu) << sh;
+			B[i] ^= (B[i] & mu) << sh;
+		}
+	}
+}
+
 // once per CTA: tile-independent tables
 B2_HD void bottom_prologue(const BottomParams& B, BottomSmem& bs, int tid, int nthreads, const uint32_t* consts) {
 	for (int i = tid; i < 160; i += nthreads) bs.LT[i] = B.lane_tw[i];
 	for (int i = tid; i < 64; i += nthreads) bs.rows[i] = lane_row_entry(i);
+	if (tid < B.n_inline) in_line_split_tables(B, bs, tid, consts);
 	for (int idx = tid; idx < 512; idx += nthreads) {
 		if (idx == 0) {
 			bs.TL[0] = 0;
@@ -126,8 +200,12 @@ B2_HD void bottom_phase_b(const BottomParams& B, const BottomSmem& bs, int warp,
 				transpose32(V);
 			}
 #pragma unroll 1
-			for (int s = 0; s < L0; s++)
-				in_line_dispatch<true>(B.cls[s], U, V, s + B.lane_shift, bs.LT + s * 32, bs.IH[s] ^ bs.IL[s * 512 + l_u], bs.IH[s] ^ bs.IL[s * 512 + l_v]);
+			for (int s = 0; s < L0; s++) {
+				if (bs.CW[80 + s])
+					butterfly_in_line_split<true>(U, V, s + B.lane_shift, bs.CW + s * 16, bs.IH[s] ^ bs.IL[s * 512 + l_u], bs.rows);
+				else
+					in_line_dispatch<true>(B.cls[s], U, V, s + B.lane_shift, bs.LT + s * 32, bs.IH[s] ^ bs.IL[s * 512 + l_u], bs.IH[s] ^ bs.IL[s * 512 + l_v]);
+			}
 		}
 		const uint32_t w = bs.TH[b] ^ bs.TL[(1 << (8 - b)) + (l_u >> (b + 1))];
 		// twiddles differ per lane: class 5 through the static GF(16) row table (IMAD + LOP3), smaller classes two-sided
@@ -138,8 +216,12 @@ B2_HD void bottom_phase_b(const BottomParams& B, const BottomSmem& bs, int warp,
 			uniform_dispatch<INV>(cls, U, V, w);
 		if (!INV && n == nline - 1) {  // last touch: the in-line layers downwards, then the compact image
 #pragma unroll 1
-			for (int s = L0 - 1; s >= 0; s--)
-				in_line_dispatch<false>(B.cls[s], U, V, s + B.lane_shift, bs.LT + s * 32, bs.IH[s] ^ bs.IL[s * 512 + l_u], bs.IH[s] ^ bs.IL[s * 512 + l_v]);
+			for (int s = L0 - 1; s >= 0; s--) {
+				if (bs.CW[80 + s])
+					butterfly_in_line_split<false>(U, V, s + B.lane_shift, bs.CW + s * 16, bs.IH[s] ^ bs.IL[s * 512 + l_u], bs.rows);
+				else
+					in_line_dispatch<false>(B.cls[s], U, V, s + B.lane_shift, bs.LT + s * 32, bs.IH[s] ^ bs.IL[s * 512 + l_u], bs.IH[s] ^ bs.IL[s * 512 + l_v]);
+			}
 			if (!P.dst_sliced) {
 				transpose32(U);
 				transpose32(V);
