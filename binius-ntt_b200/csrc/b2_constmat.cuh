@@ -208,6 +208,40 @@ B2_HD void butterfly_lane(uint32_t* U, uint32_t* V, uint32_t w, const Coef4* row
 	}
 }
 
+// the same for a twiddle of class HW (w < 2^(2^HW)): chunks of 2^HW planes, the leaves of the low digits only
+template <int HW, bool INV>
+B2_HD void butterfly_lane_cls(uint32_t* U, uint32_t* V, uint32_t w, const Coef4* rows) {
+	if (INV) {
+#pragma unroll
+		for (int i = 0; i < 32; i++) V[i] ^= U[i];
+	}
+	if constexpr (HW >= 2) {
+		constexpr int C = 1 << HW;
+		const LaneTwiddle tw(w, rows);
+#pragma unroll
+		for (int ch = 0; ch < 32 / C; ch++) {
+			uint32_t p[C];
+			LaneMul<HW, 0>::mul(V + ch * C, tw, p);
+#pragma unroll
+			for (int i = 0; i < C; i++) U[ch * C + i] ^= p[i];
+		}
+	}
+	if (!INV) {
+#pragma unroll
+		for (int i = 0; i < 32; i++) V[i] ^= U[i];
+	}
+}
+template <bool INV>
+B2_HD void butterfly_lane_dispatch(int cls, uint32_t* U, uint32_t* V, uint32_t w, const Coef4* rows) {
+	switch (cls) {
+		case 0: butterfly_lane_cls<0, INV>(U, V, w, rows); break;
+		case 2: butterfly_lane_cls<2, INV>(U, V, w, rows); break;
+		case 3: butterfly_lane_cls<3, INV>(U, V, w, rows); break;
+		case 4: butterfly_lane_cls<4, INV>(U, V, w, rows); break;
+		default: butterfly_lane<INV>(U, V, w, rows); break;
+	}
+}
+
 template <bool INV>
 B2_HD void butterfly_mat_dispatch(int cls, uint32_t* U, uint32_t* V, const Coef4* c) {
 	switch (cls) {

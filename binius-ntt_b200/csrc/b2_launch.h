@@ -26,6 +26,7 @@ struct TinyParams {
 
 int launch_pass(const PassParams& P, cudaStream_t stream);
 int launch_upper(const UpperParams& U, cudaStream_t stream);  // b2_upper.cu
+int launch_upper_pipe(const UpperParams& U, cudaStream_t stream);  // b2_upper_pipe.cu: k = 4, 6 as a producer / consumer pipeline
 int launch_bottom(const BottomParams& B, cudaStream_t stream);  // b2_bottom.cu
 int launch_bsl(const BslParams& L, cudaStream_t stream);        // b2_bsl.cu
 int launch_tiny_fanout(const TinyParams& T, cudaStream_t stream);

@@ -246,7 +246,7 @@ B2_HD void line_store(uint32_t* p, const uint32_t* w) {
 //   last : the slots are copied to the pass output afterwards (transpose back for a compact output)
 //   NT   : "no table": every layer is of class 5 and the butterfly takes the twiddle WORD (sm.tw) through the static GF(16)
 //          rows (butterfly_lane), so the caller does not build sm.leaves at all
-template <bool INV, bool NT = false>
+template <bool INV, int NT = 0>
 B2_HD void upper_pair(const UpperParams& P, const UpperSmem& sm, int lane, int xbase, int xshift, int slot_off, int b1, bool first, bool last) {
 	const int k = P.k, ls = P.ls, l = lane & ((1 << ls) - 1);  // the lane's line inside every super-line it meets
 #pragma unroll 1
@@ -267,7 +267,9 @@ B2_HD void upper_pair(const UpperParams& P, const UpperSmem& sm, int lane, int x
 				transpose32(U);
 				transpose32(V);
 			}
-			if (NT)
+			if (NT == 2)  // no table, any class (the pipelined upper pass keeps no coefficient rows)
+				butterfly_lane_dispatch<INV>(cls, U, V, sm.tw[upper_tw_index(k, bit, xu)], sm.rows16);
+			else if (NT)
 				butterfly_lane<INV>(U, V, sm.tw[upper_tw_index(k, bit, xu)], sm.rows16);
 			else
 				butterfly_mat_dispatch<INV>(cls, U, V, sm.leaves + P.lpitch * upper_tw_index(k, bit, xu));

@@ -157,7 +157,13 @@ static int run(b2ntt_plan* p, const void* d_in, void* d_out, bool inverse, int c
 		const int kind = (inverse ? hp.passes[np - 1 - n] : hp.passes[n]).kind;
 		if (kind == 1) {
 			plan_fill_upper(hp, U, n, src, dst, p->d_consts, inverse, coset, one_coset);
-			if (launch_upper(U, st)) return cuda_fail(cudaGetLastError(), "launch_upper");
+			// B2NTT_UPPER_PIPE=1: the producer / consumer form of the k = 4, 6 passes (b2_upper_pipe.cu); measured slower than
+			// upper_kernel (4.36 / 5.13 / 4.62 ms against 3.80 / 4.32 / 3.92 on the headline transform), so it is opt-in
+			const char* pe = getenv("B2NTT_UPPER_PIPE");
+			if (pe && atoi(pe) != 0 && U.k >= 4 && U.n_groups >= 512) {
+				if (launch_upper_pipe(U, st)) return cuda_fail(cudaGetLastError(), "launch_upper_pipe");
+			} else if (launch_upper(U, st))
+				return cuda_fail(cudaGetLastError(), "launch_upper");
 		} else if (kind == 2) {
 			plan_fill_bottom(hp, B, n, src, dst, p->d_consts, p->d_lane_tw, inverse, coset, one_coset);
 			if (launch_bottom(B, st)) return cuda_fail(cudaGetLastError(), "launch_bottom");

@@ -254,6 +254,26 @@ def test_tile_schedule_bitsliced_limb0_digest(b2, oracle, cuda, log_h):
     assert oracle.md5_hex(_host(y.view(-1, 4)[:, 0].contiguous())) == oracle.golden_md5(0, log_h)
 
 
+@pytest.mark.parametrize("field_bits,log_h", [(128, 23), (32, 26), (128, 25)])
+def test_pipelined_upper_passes_equal_the_default_kernels(b2, cuda, monkeypatch, field_bits, log_h):
+    """B2NTT_UPPER_PIPE=1 (b2_upper_pipe.cu: producer warp + mbarrier ring, table-free butterflies of every class) must give the
+    same words as upper_kernel, forward and inverse, on the upper + tile schedule"""
+    import torch
+
+    monkeypatch.setenv("B2NTT_UPPER", "2")
+    limbs = field_bits // 32
+    x = torch.randint(-2**31, 2**31 - 1, ((1 << log_h) * limbs,), dtype=torch.int32, device=cuda,
+                      generator=torch.Generator(device=cuda).manual_seed(field_bits + log_h))
+    plan = b2.Plan(field_bits, log_h, 0)
+    monkeypatch.delenv("B2NTT_UPPER_PIPE", raising=False)
+    y0 = plan.exec(x.clone())
+    monkeypatch.setenv("B2NTT_UPPER_PIPE", "1")
+    y1 = plan.exec(x.clone())
+    assert torch.equal(y0, y1)
+    assert torch.equal(plan.exec_inverse(y1), x)
+    plan.close()
+
+
 def test_wrong_device_pointers_are_rejected(b2, cuda):
     """a plan is bound to one device: host pointers and tensors of another GPU are refused, and no ABI call changes the
     caller's current device"""
