@@ -246,9 +246,66 @@ B2_HD void line_store(uint32_t* p, const uint32_t* w) {
 //   last : the slots are copied to the pass output afterwards (transpose back for a compact output)
 //   NT   : "no table": every layer is of class 5 and the butterfly takes the twiddle WORD (sm.tw) through the static GF(16)
 //          rows (butterfly_lane), so the caller does not build sm.leaves at all
+// A layer pair whose twiddles are both of class <= 2 (GF(16) scalars or 0 / 1: the top stages of a large transform): the
+// circuits are a few dozen instructions, so the lane's 4 lines stay in registers across both layers and cross the shared
+// memory once instead of twice.  (With class 4 / 5 circuits the same form spills: profiles/README.md, upper_quad.)
+template <bool INV>
+B2_HD void small_butterfly(int cls, uint32_t* U, uint32_t* V, const Coef4* c) {
+	if (cls == 2)
+		butterfly_mat<2, INV>(U, V, c);
+	else
+		butterfly_mat<0, INV>(U, V, c);
+}
+template <bool INV>
+B2_HD void upper_quad_small(const UpperParams& P, const UpperSmem& sm, int lane, int xbase, int xshift, int slot_off, int b1, bool first, bool last) {
+	const int k = P.k, ls = P.ls, l = lane & ((1 << ls) - 1);
+	uint32_t* s0 = sm.slots + ((size_t)((slot_off + xbase) << ls) + l) * kUSlotWords;
+	const size_t sa = ((size_t)1 << (xshift + ls)) * kUSlotWords;  // slot stride of a
+	uint32_t X0[32], X1[32], X2[32], X3[32];
+	line_load(s0, X0);
+	line_load(s0 + sa, X1);
+	line_load(s0 + 2 * sa, X2);
+	line_load(s0 + 3 * sa, X3);
+	if (first && !P.src_sliced) {
+		transpose32(X0);
+		transpose32(X1);
+		transpose32(X2);
+		transpose32(X3);
+	}
+	const int ct = P.cls[b1], cl = P.cls[b1 - 1];
+	const Coef4* tt = sm.leaves + P.lpitch * upper_tw_index(k, b1, xbase);  // one twiddle for both pairs of the top layer
+	const Coef4* t0 = sm.leaves + P.lpitch * upper_tw_index(k, b1 - 1, xbase);
+	const Coef4* t1 = sm.leaves + P.lpitch * upper_tw_index(k, b1 - 1, xbase | (2 << xshift));
+	if (!INV) {
+		small_butterfly<false>(ct, X0, X2, tt);
+		small_butterfly<false>(ct, X1, X3, tt);
+		small_butterfly<false>(cl, X0, X1, t0);
+		small_butterfly<false>(cl, X2, X3, t1);
+	} else {
+		small_butterfly<true>(cl, X0, X1, t0);
+		small_butterfly<true>(cl, X2, X3, t1);
+		small_butterfly<true>(ct, X0, X2, tt);
+		small_butterfly<true>(ct, X1, X3, tt);
+	}
+	if (last && !P.dst_sliced) {
+		transpose32(X0);
+		transpose32(X1);
+		transpose32(X2);
+		transpose32(X3);
+	}
+	line_store(s0, X0);
+	line_store(s0 + sa, X1);
+	line_store(s0 + 2 * sa, X2);
+	line_store(s0 + 3 * sa, X3);
+}
+
 template <bool INV, int NT = 0>
 B2_HD void upper_pair(const UpperParams& P, const UpperSmem& sm, int lane, int xbase, int xshift, int slot_off, int b1, bool first, bool last) {
 	const int k = P.k, ls = P.ls, l = lane & ((1 << ls) - 1);  // the lane's line inside every super-line it meets
+	if (NT == 0 && P.cls[b1] <= 2 && P.cls[b1 - 1] <= 2) {
+		upper_quad_small<INV>(P, sm, lane, xbase, xshift, slot_off, b1, first, last);
+		return;
+	}
 #pragma unroll 1
 	for (int step = 0; step < 2; step++) {
 		const bool top = INV ? step == 1 : step == 0;  // which of the two layers
