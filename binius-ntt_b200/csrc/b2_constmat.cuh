@@ -109,16 +109,17 @@ B2_HD Coef4 coef_row(uint32_t lam, int i) {
 }
 
 // U ^= w * V ; V ^= U  (forward) or  V ^= U ; U ^= w * V  (inverse); w of class HW given by its coefficient rows
-template <int HW, bool INV, int NI = kMatImadTerms>
+// NP = planes of the operands: 32 (a whole bundle) or 16 (one half of it -- a product of class <= 4 never mixes the halves)
+template <int HW, bool INV, int NI = kMatImadTerms, int NP = 32>
 B2_HD void butterfly_mat(uint32_t* U, uint32_t* V, const Coef4* c) {
 	if (INV) {
 #pragma unroll
-		for (int i = 0; i < 32; i++) V[i] ^= U[i];
+		for (int i = 0; i < NP; i++) V[i] ^= U[i];
 	}
 	if constexpr (HW >= 2) {
 		constexpr int C = 1 << HW;
 #pragma unroll
-		for (int ch = 0; ch < 32 / C; ch++) {
+		for (int ch = 0; ch < NP / C; ch++) {
 			uint32_t p[C];
 			MatMul<HW, NI>::mul(V + ch * C, c, p);
 #pragma unroll
@@ -127,7 +128,17 @@ B2_HD void butterfly_mat(uint32_t* U, uint32_t* V, const Coef4* c) {
 	}
 	if (!INV) {
 #pragma unroll
-		for (int i = 0; i < 32; i++) V[i] ^= U[i];
+		for (int i = 0; i < NP; i++) V[i] ^= U[i];
+	}
+}
+// two butterflies of one class (<= 4) on half bundles behind one dispatch
+template <bool INV>
+B2_HD void butterfly_half_dispatch2(int cls, uint32_t* U0, uint32_t* V0, const Coef4* c0, uint32_t* U1, uint32_t* V1, const Coef4* c1) {
+	switch (cls) {
+		case 0: butterfly_mat<0, INV, kMatImadTerms, 16>(U0, V0, c0), butterfly_mat<0, INV, kMatImadTerms, 16>(U1, V1, c1); break;
+		case 2: butterfly_mat<2, INV, kMatImadTerms, 16>(U0, V0, c0), butterfly_mat<2, INV, kMatImadTerms, 16>(U1, V1, c1); break;
+		case 3: butterfly_mat<3, INV, kMatImadTerms, 16>(U0, V0, c0), butterfly_mat<3, INV, kMatImadTerms, 16>(U1, V1, c1); break;
+		default: butterfly_mat<4, INV, kMatImadTerms, 16>(U0, V0, c0), butterfly_mat<4, INV, kMatImadTerms, 16>(U1, V1, c1); break;
 	}
 }
 // ---- the same product for a twiddle that is private to the THREAD (the per-lane layers of the tile pass) -------------------------

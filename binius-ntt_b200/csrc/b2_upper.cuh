@@ -299,11 +299,68 @@ B2_HD void upper_quad_small(const UpperParams& P, const UpperSmem& sm, int lane,
 	line_store(s0 + 3 * sa, X3);
 }
 
+// A layer pair of class <= 4 on bundles that need no transpose in this call: the product never mixes planes 0..15 with
+// planes 16..31, so the pair runs on the lower halves of the lane's 4 lines, then on the upper halves -- 64 data registers at
+// a time, and every line crosses the shared memory once per layer PAIR.
+B2_HD void half_load(const uint32_t* p, uint32_t* w) {
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+	for (int g = 0; g < 4; g++) {
+		const uint4 v = reinterpret_cast<const uint4*>(p)[g];
+		w[4 * g] = v.x, w[4 * g + 1] = v.y, w[4 * g + 2] = v.z, w[4 * g + 3] = v.w;
+	}
+#else
+	for (int j = 0; j < 16; j++) w[j] = p[j];
+#endif
+}
+B2_HD void half_store(uint32_t* p, const uint32_t* w) {
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+	for (int g = 0; g < 4; g++) reinterpret_cast<uint4*>(p)[g] = make_uint4(w[4 * g], w[4 * g + 1], w[4 * g + 2], w[4 * g + 3]);
+#else
+	for (int j = 0; j < 16; j++) p[j] = w[j];
+#endif
+}
+template <bool INV>
+B2_HD void upper_quad_halves(const UpperParams& P, const UpperSmem& sm, int lane, int xbase, int xshift, int slot_off, int b1) {
+	const int k = P.k, ls = P.ls, l = lane & ((1 << ls) - 1);
+	uint32_t* s0 = sm.slots + ((size_t)((slot_off + xbase) << ls) + l) * kUSlotWords;
+	const size_t sa = ((size_t)1 << (xshift + ls)) * kUSlotWords;  // slot stride of a
+	const int ct = P.cls[b1], cl = P.cls[b1 - 1];
+	const Coef4* tt = sm.leaves + P.lpitch * upper_tw_index(k, b1, xbase);  // one twiddle for both pairs of the top layer
+	const Coef4* t0 = sm.leaves + P.lpitch * upper_tw_index(k, b1 - 1, xbase);
+	const Coef4* t1 = sm.leaves + P.lpitch * upper_tw_index(k, b1 - 1, xbase | (2 << xshift));
+#pragma unroll 1
+	for (int h = 0; h < 2; h++) {
+		uint32_t* s = s0 + 16 * h;
+		uint32_t X0[16], X1[16], X2[16], X3[16];
+		half_load(s, X0);
+		half_load(s + sa, X1);
+		half_load(s + 2 * sa, X2);
+		half_load(s + 3 * sa, X3);
+		if (!INV) {
+			butterfly_half_dispatch2<false>(ct, X0, X2, tt, X1, X3, tt);
+			butterfly_half_dispatch2<false>(cl, X0, X1, t0, X2, X3, t1);
+		} else {
+			butterfly_half_dispatch2<true>(cl, X0, X1, t0, X2, X3, t1);
+			butterfly_half_dispatch2<true>(ct, X0, X2, tt, X1, X3, tt);
+		}
+		half_store(s, X0);
+		half_store(s + sa, X1);
+		half_store(s + 2 * sa, X2);
+		half_store(s + 3 * sa, X3);
+	}
+}
+
 template <bool INV, int NT = 0>
 B2_HD void upper_pair(const UpperParams& P, const UpperSmem& sm, int lane, int xbase, int xshift, int slot_off, int b1, bool first, bool last) {
 	const int k = P.k, ls = P.ls, l = lane & ((1 << ls) - 1);  // the lane's line inside every super-line it meets
 	if (NT == 0 && P.cls[b1] <= 2 && P.cls[b1 - 1] <= 2) {
 		upper_quad_small<INV>(P, sm, lane, xbase, xshift, slot_off, b1, first, last);
+		return;
+	}
+	if (NT == 0 && P.cls[b1] <= 4 && P.cls[b1 - 1] <= 4 && !(first && !P.src_sliced) && !(last && !P.dst_sliced)) {
+		upper_quad_halves<INV>(P, sm, lane, xbase, xshift, slot_off, b1);
 		return;
 	}
 #pragma unroll 1
