@@ -27,6 +27,7 @@
 // indexing is checked in a container without a GPU.
 #pragma once
 #include "b2_bundle.cuh"
+#include "b2_constmat.cuh"
 
 namespace b2 {
 
@@ -85,12 +86,14 @@ struct PassSmem {
 	uint32_t* slots;    // [2T][32]
 	uint32_t* inl_lo;   // [5][2T] in-line layers, by line x of the tile
 	uint32_t* inl_hi;   // [5][T]  in-line layers, by tile of the group
+	Coef4* rows;        // [4][16] static GF(16) coefficient rows of butterfly_lane_dispatch (b2_constmat.cuh)
 };
-B2_HD size_t pass_smem_words(int G, int in_line) { return 160 + G + G / 2 + kSlotWords * (size_t)G + (in_line ? 5 * (size_t)G + 5 * (size_t)G / 2 : 0); }
+B2_HD size_t pass_smem_words(int G, int in_line) { return 256 + 160 + G + G / 2 + kSlotWords * (size_t)G + (in_line ? 5 * (size_t)G + 5 * (size_t)G / 2 : 0); }
 B2_HD PassSmem pass_smem_view(uint32_t* base, int G) {
 	PassSmem sm;
 	sm.slots = base;  // first: 16-byte aligned for the vector accesses
-	sm.lane_tw = sm.slots + kSlotWords * (size_t)G;
+	sm.rows = reinterpret_cast<Coef4*>(sm.slots + kSlotWords * (size_t)G);  // 16-byte aligned: kSlotWords is a multiple of 4
+	sm.lane_tw = sm.slots + kSlotWords * (size_t)G + 256;
 	sm.tw_lo = sm.lane_tw + 160;
 	sm.tw_hi = sm.tw_lo + G;
 	sm.inl_lo = sm.tw_hi + G / 2;
@@ -118,6 +121,7 @@ B2_HD int pass_stage(const PassParams& P, int i) { return P.n_inline + P.q0 - P.
 B2_HD void pass_prologue(const PassParams& P, PassSmem& sm, int tid) {
 	const int T = P.cta_threads;
 	for (int i = tid; i < 5 * 32; i += T) sm.lane_tw[i] = P.lane_tw[i];
+	for (int i = tid; i < 64; i += T) sm.rows[i] = lane_row_entry(i);
 	for (int idx = tid; idx < (1 << P.k); idx += T) {
 		if (idx == 0) {
 			sm.tw_lo[0] = 0;
@@ -355,7 +359,7 @@ B2_HD void pass_layer(const PassParams& P, PassSmem& sm, uint64_t group, int tid
 		if (INV && P.in_line) in_line_layers<true>(P, sm, st, c.tile_in_group, xu, xv);
 	}
 	const uint32_t w = sm.tw_hi[c.tile_in_group * P.k + i] ^ sm.tw_lo[(1 << (P.k - 1 - i)) + (c.t >> i)];
-	uniform_dispatch<INV>(P.cls[pass_stage(P, i)], st.A, st.B, w);
+	butterfly_lane_dispatch<INV>(P.cls[pass_stage(P, i)], st.A, st.B, w, sm.rows);  // two-pipe product, any class (round 1: uniform_dispatch)
 	if (last) {
 		if (!INV && P.in_line) in_line_layers<false>(P, sm, st, c.tile_in_group, xu, xv);
 		if (!P.dst_sliced) {

@@ -71,7 +71,7 @@ extern "C" int b2ntt_plan_create(b2ntt_plan** out, int field_bits, int layout, i
 	if (const char* e = getenv("B2NTT_GROUP_LINES")) glines = atoi(e);  // tuning knob: 128, 256 or 512
 	// schedule: the upper + tile passes win from 2^21 lines (256 MiB) of total work; below, the bundle passes (smaller
 	// groups, fewer launches) fill the SMs better (profiles/r1w_*: 1.5x at log_h = 20 GF(2^32); round-2 kernels, profiles/
-	// r2z_schedule_sweep.log: 2^21 lines 1.62 vs 1.79 ms (GF128) and 1.95 vs 2.02 ms (GF32), 2^20 lines 0.93 vs 0.92 and 1.12 vs 1.02)
+	// r2z_schedule_sweep.log: 2^21 lines 1.62 vs 1.72 ms (GF128) and 1.95 vs 1.94 ms (GF32), 2^20 lines 0.91 vs 0.84 and 1.11 vs 0.95)
 	const int line_bits = log_h + log_rate + (field_bits == 128 ? 2 : 0) - 5;
 	const uint64_t total_lines = (uint64_t)(batch > 0 ? batch : 1) << (line_bits > 0 ? line_bits : 0);
 	int upper = total_lines >= (uint64_t(1) << 21) ? 2 : 0;
