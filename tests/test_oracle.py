@@ -135,10 +135,13 @@ def test_bb31_oracle_matches_reference_digests(oracle):
 @pytest.fixture(scope="module")
 def emul():
     p = os.path.join(ROOT, "tests", "emul", "libb2emul.so")
-    if not os.path.exists(p):
-        import subprocess
+    import shutil
+    import subprocess
 
-        subprocess.run(["make", "-C", os.path.dirname(p)], check=True)
+    # the emulator compiles the kernels' own phase functions: rebuild whenever a header under csrc/ is newer (make decides), so
+    # these tests never run a stale copy; on a box without make / g++ the prebuilt library that travelled with the repo is used
+    if shutil.which("make") and shutil.which("g++"):
+        subprocess.run(["make", "-s", "-C", os.path.dirname(p)], check=True)
     E = C.CDLL(p)
     u32p = np.ctypeslib.ndpointer(dtype=np.uint32, flags="C_CONTIGUOUS")
     E.emul_antt.argtypes = [C.c_int] * 5 + [u32p, u32p, C.c_int, C.c_int]
