@@ -31,15 +31,16 @@ struct BottomSmem {
 	uint32_t* IL;   // [n_inline][512] in-line twiddle by local line
 	uint32_t* LT;   // [5][32] lane_tw copy
 	Coef4* rows;    // [4][16] the GF(16) coefficient rows of butterfly_lane (b2_constmat.cuh)
-	uint32_t* CW;   // [5][16] position masks of the GF(16) correction of butterfly_in_line_split; [80 + s] = 1: stage s uses it
+	uint32_t* CW;   // [5][16] position masks of the GF(16) correction of butterfly_in_line_split; [80 + s] = 1: stage s uses it;
+	                // [85] = 1: the three in-line layers run in the exchanged form (in_line_stage_swapped), masks at [96 + 16 s]
 };
 // One CTA runs kBottomTeams teams of 4 warps, each on its own tile.  Warps w and w + 4 share an SM sub-partition and
 // meet at the same CTA barriers, so they execute the same stretch of straight-line butterfly code at the same time:
 // the instruction cache serves both (two independent CTAs per SM ran out of phase and stalled on instruction fetch).
-// layout: [consts 1024][TL 512][IL 5*512][LT 160][rows 256][CW 96]  then per team  [coefficient rows 15*108*4][tw 16][TH 8][IH 8][slots 16*32*36]
+// layout: [consts 1024][TL 512][IL 5*512][LT 160][rows 256][CW 160]  then per team  [coefficient rows 15*108*4][tw 16][TH 8][IH 8][slots 16*32*36]
 constexpr int kBottomTeams = 2;
 B2_HD size_t bottom_team_words() { return (size_t)kUpperMaxTw * kLeafPitch + 16 + 8 + 8 + (size_t)16 * 32 * kUSlotWords; }
-B2_HD size_t bottom_smem_words() { return 1024 + 512 + 5 * 512 + 160 + 256 + 96 + kBottomTeams * bottom_team_words(); }
+B2_HD size_t bottom_smem_words() { return 1024 + 512 + 5 * 512 + 160 + 256 + 160 + kBottomTeams * bottom_team_words(); }
 B2_HD BottomSmem bottom_smem_view(uint32_t* base, int team = 0) {
 	BottomSmem b;
 	b.us.consts = base;
@@ -49,7 +50,7 @@ B2_HD BottomSmem bottom_smem_view(uint32_t* base, int team = 0) {
 	b.rows = reinterpret_cast<Coef4*>(b.LT + 160);  // 16-byte aligned: 1024 + 512 + 2560 + 160 words before it
 	b.us.rows16 = b.rows;                           // the same table serves the coefficient-table build of phase A
 	b.CW = b.LT + 160 + 256;
-	uint32_t* t = b.CW + 96 + (size_t)team * bottom_team_words();
+	uint32_t* t = b.CW + 160 + (size_t)team * bottom_team_words();
 	b.us.leaves = reinterpret_cast<Coef4*>(t);
 	b.us.tw = t + kUpperMaxTw * kLeafPitch;
 	b.TH = b.us.tw + 16;
@@ -137,11 +138,125 @@ B2_HD void butterfly_in_line_split(uint32_t* A, uint32_t* B, int p, const uint32
 	}
 }
 
+// ---- the in-line layers of the compact GF(2^128) image in EXCHANGED form -------------------------------------------------------
+// butterfly_in_line_split still pays for the layout: the partner of a position sits 2^p positions higher in the SAME word, so every
+// layer shifts the upper halves of one bundle down, scatters the product back and shifts the sum up again (about 290 ALU
+// instructions per layer).  Instead, before layer p the two bundles exchange halves (an involution: 1 PRMT per word for the
+// byte-sized layers):  A' = A[bit p clear] | B[bit p clear] << 2^p,  B' = A[bit p set] >> 2^p | B[bit p set].
+// A' then holds every u position of both lines and B' every v position, in the same places: the layer is the plain butterfly
+// A' ^= W * B' ; B' ^= A'.  The exchanges are not undone between the layers -- layer p - 1 exchanges (A', B') on its own bit --
+// so after the three layers position bit 4 of a bundle tells the LINE, bits 3 and 2 the element bits e2 and e1, and the bundle
+// (A or B) the element bit e0.  That permutation moves whole elements (16-byte chunks), so it costs nothing: the transposed words
+// are stored chunk by chunk to where they belong (swapped_store), and the inverse transform loads them the same way.
+// The twiddle of position pos at stage s (p = s + 2) is wa ^ D_s(pos), D_s = XOR_j (bit p + j of pos) * C[s][j], j = 0 .. 2 - s:
+// the element bits above the stage and the line bit, exactly the index bits the thread-uniform wa (line A, element 0) leaves out.
+B2_HD void exchange_halves(uint32_t* A, uint32_t* B, int p) {
+#if defined(__CUDA_ARCH__)
+	if (p == 4) {
+#pragma unroll
+		for (int i = 0; i < 32; i++) {
+			const uint32_t a = A[i], b = B[i];
+			A[i] = __byte_perm(a, b, 0x5410), B[i] = __byte_perm(a, b, 0x7632);
+		}
+		return;
+	}
+	if (p == 3) {
+#pragma unroll
+		for (int i = 0; i < 32; i++) {
+			const uint32_t a = A[i], b = B[i];
+			A[i] = __byte_perm(a, b, 0x6240), B[i] = __byte_perm(a, b, 0x7351);
+		}
+		return;
+	}
+#endif
+	const int sh = 1 << p;
+	const uint32_t mu = lane_mask_lo(p);
+#pragma unroll
+	for (int i = 0; i < 32; i++) {
+		const uint32_t a = A[i], b = B[i];
+		A[i] = (a & mu) | ((b & mu) << sh), B[i] = ((a >> sh) & mu) | (b & ~mu);
+	}
+}
+template <bool INVERSE>
+B2_HD void in_line_stage_swapped(uint32_t* A, uint32_t* B, int p, const uint32_t* cw, uint32_t wa, const Coef4* rows) {
+	if (!INVERSE) exchange_halves(A, B, p);
+	if (INVERSE) {
+#pragma unroll
+		for (int i = 0; i < 32; i++) B[i] ^= A[i];
+	}
+	{
+		uint32_t Pr[32], c[16];
+		const LaneTwiddle tw(wa, rows);
+		LaneMul<5, 0>::mul(B, tw, Pr);
+#pragma unroll
+		for (int i = 0; i < 16; i++) c[i] = cw[i];
+#pragma unroll
+		for (int g = 0; g < 8; g++) {
+#pragma unroll
+			for (int i = 0; i < 4; i++)
+				A[4 * g + i] ^= Pr[4 * g + i] ^ (B[4 * g] & c[4 * i]) ^ (B[4 * g + 1] & c[4 * i + 1]) ^ (B[4 * g + 2] & c[4 * i + 2]) ^ (B[4 * g + 3] & c[4 * i + 3]);
+		}
+	}
+	if (!INVERSE) {
+#pragma unroll
+		for (int i = 0; i < 32; i++) B[i] ^= A[i];
+	}
+	if (INVERSE) exchange_halves(A, B, p);
+}
+// chunk c = (line, e2, e1) of bundle A / B <-> element (e2, e1, 0 / 1) of line lu / lv
+B2_HD void swapped_store(uint32_t* su, uint32_t* sv, const uint32_t* A, const uint32_t* B) {
+#pragma unroll
+	for (int c = 0; c < 8; c++) {
+		uint32_t* d = (c & 4 ? sv : su) + 8 * (c & 3);
+#if defined(__CUDA_ARCH__)
+		reinterpret_cast<uint4*>(d)[0] = make_uint4(A[4 * c], A[4 * c + 1], A[4 * c + 2], A[4 * c + 3]);
+		reinterpret_cast<uint4*>(d)[1] = make_uint4(B[4 * c], B[4 * c + 1], B[4 * c + 2], B[4 * c + 3]);
+#else
+		for (int j = 0; j < 4; j++) d[j] = A[4 * c + j], d[4 + j] = B[4 * c + j];
+#endif
+	}
+}
+B2_HD void swapped_load(const uint32_t* su, const uint32_t* sv, uint32_t* A, uint32_t* B) {
+#pragma unroll
+	for (int c = 0; c < 8; c++) {
+		const uint32_t* d = (c & 4 ? sv : su) + 8 * (c & 3);
+#if defined(__CUDA_ARCH__)
+		const uint4 x = reinterpret_cast<const uint4*>(d)[0], y = reinterpret_cast<const uint4*>(d)[1];
+		A[4 * c] = x.x, A[4 * c + 1] = x.y, A[4 * c + 2] = x.z, A[4 * c + 3] = x.w;
+		B[4 * c] = y.x, B[4 * c + 1] = y.y, B[4 * c + 2] = y.z, B[4 * c + 3] = y.w;
+#else
+		for (int j = 0; j < 4; j++) A[4 * c + j] = d[j], B[4 * c + j] = d[4 + j];
+#endif
+	}
+}
+// one thread: can the exchanged form be used (compact GF(2^128) image, class-5 stages, GF(16) constants), and its masks
+B2_HD void in_line_swap_tables(const BottomParams& B, BottomSmem& bs, const uint32_t* consts) {
+	bool ok = B.n_inline == 3 && B.lane_shift == 2 && B.batch_bits == 0;
+	for (int s = 0; s < 3 && ok; s++) {
+		uint32_t D[4] = {0, 0, 0, 0};
+		if (B.cls[s] != 5) ok = false;
+		for (int j = 0; j <= 2 - s; j++) {
+			const uint32_t c = consts[s * 32 + j], m = ~lane_mask_lo(s + 2 + j);
+			if (c >= 16u) ok = false;
+			for (int r = 0; r < 4; r++) D[r] ^= bitmask(c, r) & m;
+		}
+		for (int i = 0; i < 4; i++)
+			for (int k = 0; k < 4; k++) {
+				uint32_t m = 0;
+				for (int r = 0; r < 4; r++)
+					if ((Tower<2>::mul(1u << r, 1u << k) >> i) & 1u) m ^= D[r];
+				bs.CW[96 + s * 16 + 4 * i + k] = m;
+			}
+	}
+	bs.CW[85] = ok ? 1u : 0u;
+}
+
 // once per CTA: tile-independent tables
 B2_HD void bottom_prologue(const BottomParams& B, BottomSmem& bs, int tid, int nthreads, const uint32_t* consts) {
 	for (int i = tid; i < 160; i += nthreads) bs.LT[i] = B.lane_tw[i];
 	for (int i = tid; i < 64; i += nthreads) bs.rows[i] = lane_row_entry(i);
 	if (tid < B.n_inline) in_line_split_tables(B, bs, tid, consts);
+	if (tid == 8) in_line_swap_tables(B, bs, consts);
 	for (int idx = tid; idx < 512; idx += nthreads) {
 		if (idx == 0) {
 			bs.TL[0] = 0;
@@ -191,14 +306,24 @@ B2_HD void bottom_phase_b(const BottomParams& B, const BottomSmem& bs, int warp,
 		const int lu = ((tt >> b) << (b + 1)) | (tt & ((1 << b) - 1)), lv = lu | (1 << b);
 		uint32_t* su = slot0 + (size_t)lu * kUSlotWords;
 		uint32_t* sv = slot0 + (size_t)lv * kUSlotWords;
-		line_load(su, U);
-		line_load(sv, V);
+		// exchanged form of the in-line layers (in_line_stage_swapped): compact GF(2^128) images with GF(16) low constants
+		const bool swap = bs.CW[85] != 0 && (INV ? !P.src_sliced : !P.dst_sliced);
+		if (INV && n == 0 && swap)
+			swapped_load(su, sv, U, V);
+		else {
+			line_load(su, U);
+			line_load(sv, V);
+		}
 		const int l_u = (sl << 5) | lu, l_v = (sl << 5) | lv;
 		if (INV && n == 0) {  // first touch: back from the compact image, then the in-line layers upwards
 			if (!P.src_sliced) {
 				transpose32(U);
 				transpose32(V);
 			}
+			if (swap) {
+#pragma unroll 1
+				for (int s = 0; s < 3; s++) in_line_stage_swapped<true>(U, V, s + 2, bs.CW + 96 + s * 16, bs.IH[s] ^ bs.IL[s * 512 + l_u], bs.rows);
+			} else
 #pragma unroll 1
 			for (int s = 0; s < L0; s++) {
 				if (bs.CW[80 + s])
@@ -215,6 +340,10 @@ B2_HD void bottom_phase_b(const BottomParams& B, const BottomSmem& bs, int warp,
 		else
 			uniform_dispatch<INV>(cls, U, V, w);
 		if (!INV && n == nline - 1) {  // last touch: the in-line layers downwards, then the compact image
+			if (swap) {
+#pragma unroll 1
+				for (int s = 2; s >= 0; s--) in_line_stage_swapped<false>(U, V, s + 2, bs.CW + 96 + s * 16, bs.IH[s] ^ bs.IL[s * 512 + l_u], bs.rows);
+			} else
 #pragma unroll 1
 			for (int s = L0 - 1; s >= 0; s--) {
 				if (bs.CW[80 + s])
@@ -227,8 +356,12 @@ B2_HD void bottom_phase_b(const BottomParams& B, const BottomSmem& bs, int warp,
 				transpose32(V);
 			}
 		}
-		line_store(su, U);
-		line_store(sv, V);
+		if (!INV && n == nline - 1 && swap)
+			swapped_store(su, sv, U, V);
+		else {
+			line_store(su, U);
+			line_store(sv, V);
+		}
 	}
 }
 
