@@ -8,7 +8,7 @@
 
 namespace b2 {
 
-template <bool INV>
+template <bool INV, bool SWAP>
 __global__ void __launch_bounds__(kBottomTeams * 128, 1) bottom_kernel(const __grid_constant__ BottomParams B) {
 	extern __shared__ __align__(16) uint32_t bsmem_raw[];
 	const int team = threadIdx.x >> 7, tid = threadIdx.x & 127, warp = tid >> 5, lane = tid & 31, T = 128;
@@ -62,7 +62,7 @@ __global__ void __launch_bounds__(kBottomTeams * 128, 1) bottom_kernel(const __g
 			for (int iter = 0; iter < 2; iter++) {
 #pragma unroll 1
 				for (int n = 0; n < nline; n++) {
-					bottom_phase_b<INV>(B, bs, warp, lane, iter, n);
+					bottom_phase_b<INV, SWAP>(B, bs, warp, lane, iter, n);
 					__syncwarp();
 				}
 			}
@@ -88,23 +88,27 @@ __global__ void __launch_bounds__(kBottomTeams * 128, 1) bottom_kernel(const __g
 	}
 }
 
-template <bool INV>
+template <bool INV, bool SWAP>
 static int launch_bottom_t(const BottomParams& B, cudaStream_t stream) {
 	int sms = 0, dev = 0;
 	const size_t smem = bottom_smem_words() * sizeof(uint32_t);
 	cudaGetDevice(&dev);
 	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-	cudaFuncSetAttribute(bottom_kernel<INV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+	cudaFuncSetAttribute(bottom_kernel<INV, SWAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 	uint64_t ctas = (uint64_t)sms * 4;  // one CTA of two teams per SM, a few chunks each for balance
 	const uint64_t pairs = (B.up.n_groups + kBottomTeams - 1) / kBottomTeams;
 	if (ctas > pairs) ctas = pairs;
 	if (ctas == 0) return -1;
-	bottom_kernel<INV><<<(unsigned)ctas, kBottomTeams * 128, smem, stream>>>(B);
+	bottom_kernel<INV, SWAP><<<(unsigned)ctas, kBottomTeams * 128, smem, stream>>>(B);
 	return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 
 int launch_bottom(const BottomParams& B, cudaStream_t stream) {
-	return B.up.inverse ? launch_bottom_t<true>(B, stream) : launch_bottom_t<false>(B, stream);
+	// the exchanged in-line form needs the compact image on the in-line side of the pass (its element permutation is undone by the
+	// chunk-wise loads / stores of the compact words)
+	const bool swap = B.swap_inline && (B.up.inverse ? !B.up.src_sliced : !B.up.dst_sliced);
+	if (B.up.inverse) return swap ? launch_bottom_t<true, true>(B, stream) : launch_bottom_t<true, false>(B, stream);
+	return swap ? launch_bottom_t<false, true>(B, stream) : launch_bottom_t<false, false>(B, stream);
 }
 
 }  // namespace b2

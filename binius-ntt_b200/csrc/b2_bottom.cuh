@@ -21,6 +21,7 @@ struct BottomParams {
 	int lane_shift;          // in-line layer s pairs lanes differing in bit s + lane_shift
 	int batch_bits;          // low line bits that are not butterfly bits
 	uint8_t cls[32];         // twiddle class per stage
+	int swap_inline;         // 1: the in-line layers run in the exchanged form (in_line_stage_swapped); decided on the host (b2_plan.h)
 };
 
 struct BottomSmem {
@@ -32,7 +33,7 @@ struct BottomSmem {
 	uint32_t* LT;   // [5][32] lane_tw copy
 	Coef4* rows;    // [4][16] the GF(16) coefficient rows of butterfly_lane (b2_constmat.cuh)
 	uint32_t* CW;   // [5][16] position masks of the GF(16) correction of butterfly_in_line_split; [80 + s] = 1: stage s uses it;
-	                // [85] = 1: the three in-line layers run in the exchanged form (in_line_stage_swapped), masks at [96 + 16 s]
+	                // [96 + 16 s]: masks of the exchanged form (in_line_stage_swapped), when B.swap_inline
 };
 // One CTA runs kBottomTeams teams of 4 warps, each on its own tile.  Warps w and w + 4 share an SM sub-partition and
 // meet at the same CTA barriers, so they execute the same stretch of straight-line butterfly code at the same time:
@@ -229,15 +230,23 @@ B2_HD void swapped_load(const uint32_t* su, const uint32_t* sv, uint32_t* A, uin
 #endif
 	}
 }
-// one thread: can the exchanged form be used (compact GF(2^128) image, class-5 stages, GF(16) constants), and its masks
-B2_HD void in_line_swap_tables(const BottomParams& B, BottomSmem& bs, const uint32_t* consts) {
-	bool ok = B.n_inline == 3 && B.lane_shift == 2 && B.batch_bits == 0;
+// can the exchanged form be used: compact GF(2^128) image, class-5 stages, GF(16) low constants (host: b2_plan.h)
+B2_HD bool in_line_swap_ok(int n_inline, int lane_shift, int batch_bits, const uint8_t* cls, const uint32_t* consts, int pitch) {
+	bool ok = n_inline == 3 && lane_shift == 2 && batch_bits == 0;
 	for (int s = 0; s < 3 && ok; s++) {
+		if (cls[s] != 5) ok = false;
+		for (int j = 0; j <= 2 - s; j++)
+			if (consts[s * pitch + j] >= 16u) ok = false;
+	}
+	return ok;
+}
+// one thread: the masks of the exchanged form
+B2_HD void in_line_swap_tables(const BottomParams& B, BottomSmem& bs, const uint32_t* consts) {
+	if (!B.swap_inline) return;
+	for (int s = 0; s < 3; s++) {
 		uint32_t D[4] = {0, 0, 0, 0};
-		if (B.cls[s] != 5) ok = false;
 		for (int j = 0; j <= 2 - s; j++) {
 			const uint32_t c = consts[s * 32 + j], m = ~lane_mask_lo(s + 2 + j);
-			if (c >= 16u) ok = false;
 			for (int r = 0; r < 4; r++) D[r] ^= bitmask(c, r) & m;
 		}
 		for (int i = 0; i < 4; i++)
@@ -248,7 +257,6 @@ B2_HD void in_line_swap_tables(const BottomParams& B, BottomSmem& bs, const uint
 				bs.CW[96 + s * 16 + 4 * i + k] = m;
 			}
 	}
-	bs.CW[85] = ok ? 1u : 0u;
 }
 
 // once per CTA: tile-independent tables
@@ -293,7 +301,7 @@ B2_HD void bottom_tile_tables(const BottomParams& B, BottomSmem& bs, const UGrou
 // Phase B for one lane: the warp's super-lines 4*warp .. 4*warp+3, two at a time (iter; 16 lanes x 2 lines each).
 // n-th line layer in execution order, n < 5 - batch_bits; callers put __syncwarp() between layers.  The in-line
 // layers and the transposes ride on the layer that touches a line last (forward) or first (inverse).
-template <bool INV>
+template <bool INV, bool SWAP = false>
 B2_HD void bottom_phase_b(const BottomParams& B, const BottomSmem& bs, int warp, int lane, int iter, int n) {
 	const UpperParams& P = B.up;
 	const int bb = B.batch_bits, L0 = B.n_inline;
@@ -307,7 +315,7 @@ B2_HD void bottom_phase_b(const BottomParams& B, const BottomSmem& bs, int warp,
 		uint32_t* su = slot0 + (size_t)lu * kUSlotWords;
 		uint32_t* sv = slot0 + (size_t)lv * kUSlotWords;
 		// exchanged form of the in-line layers (in_line_stage_swapped): compact GF(2^128) images with GF(16) low constants
-		const bool swap = bs.CW[85] != 0 && (INV ? !P.src_sliced : !P.dst_sliced);
+		constexpr bool swap = SWAP;  // chosen by the launch: B.swap_inline and a compact image on the in-line side
 		if (INV && n == 0 && swap)
 			swapped_load(su, sv, U, V);
 		else {
@@ -320,7 +328,7 @@ B2_HD void bottom_phase_b(const BottomParams& B, const BottomSmem& bs, int warp,
 				transpose32(U);
 				transpose32(V);
 			}
-			if (swap) {
+			if constexpr (swap) {
 #pragma unroll 1
 				for (int s = 0; s < 3; s++) in_line_stage_swapped<true>(U, V, s + 2, bs.CW + 96 + s * 16, bs.IH[s] ^ bs.IL[s * 512 + l_u], bs.rows);
 			} else
@@ -340,7 +348,7 @@ B2_HD void bottom_phase_b(const BottomParams& B, const BottomSmem& bs, int warp,
 		else
 			uniform_dispatch<INV>(cls, U, V, w);
 		if (!INV && n == nline - 1) {  // last touch: the in-line layers downwards, then the compact image
-			if (swap) {
+			if constexpr (swap) {
 #pragma unroll 1
 				for (int s = 2; s >= 0; s--) in_line_stage_swapped<false>(U, V, s + 2, bs.CW + 96 + s * 16, bs.IH[s] ^ bs.IL[s * 512 + l_u], bs.rows);
 			} else

@@ -277,6 +277,7 @@ inline void plan_fill_bottom(const HostPlan& hp, BottomParams& B, int n, const u
 	B.lane_tw = lane_tw;
 	B.n_inline = hp.n_inline, B.lane_shift = hp.lane_shift, B.batch_bits = hp.batch_bits;
 	memcpy(B.cls, hp.cls, 32);
+	B.swap_inline = in_line_swap_ok(hp.n_inline, hp.lane_shift, hp.batch_bits, hp.cls, hp.consts, kConstPitch) ? 1 : 0;
 }
 
 // Parameters of the block-sliced lowest pass (kind 4).

@@ -89,7 +89,13 @@ static void run_bottom(const BottomParams& B) {
 		}
 		for (int iter = 0; iter < 2; iter++)
 			for (int n = 0; n < nline; n++)
-				for (int t = 0; t < T; t++) bottom_phase_b<INV>(B, bs, t >> 5, t & 31, iter, n);
+				for (int t = 0; t < T; t++) {
+					// as launch_bottom: the exchanged in-line form when the plan allows it and the in-line side is compact
+					if (B.swap_inline && (INV ? !P.src_sliced : !P.dst_sliced))
+						bottom_phase_b<INV, true>(B, bs, t >> 5, t & 31, iter, n);
+					else
+						bottom_phase_b<INV, false>(B, bs, t >> 5, t & 31, iter, n);
+				}
 		if (INV) {
 			for (int t = 0; t < T; t++) {
 				if (nt) upper_pair<true, true>(P, bs.us, t & 31, (t >> 5) << 2, 0, 0, 1, false, false);
