@@ -301,7 +301,7 @@ B2_HD void bottom_tile_tables(const BottomParams& B, BottomSmem& bs, const UGrou
 // Phase B for one lane: the warp's super-lines 4*warp .. 4*warp+3, two at a time (iter; 16 lanes x 2 lines each).
 // n-th line layer in execution order, n < 5 - batch_bits; callers put __syncwarp() between layers.  The in-line
 // layers and the transposes ride on the layer that touches a line last (forward) or first (inverse).
-template <bool INV, bool SWAP = false>
+template <bool INV, bool SWAP = false, bool ALL5 = false>
 B2_HD void bottom_phase_b(const BottomParams& B, const BottomSmem& bs, int warp, int lane, int iter, int n) {
 	const UpperParams& P = B.up;
 	const int bb = B.batch_bits, L0 = B.n_inline;
@@ -343,9 +343,9 @@ B2_HD void bottom_phase_b(const BottomParams& B, const BottomSmem& bs, int warp,
 		const uint32_t w = bs.TH[b] ^ bs.TL[(1 << (8 - b)) + (l_u >> (b + 1))];
 		// twiddles differ per lane: class 5 through the static GF(16) row table (IMAD + LOP3), smaller classes two-sided
 		const int cls = B.cls[bottom_stage(B, b)];
-		if (cls == 5)
+		if (ALL5 || cls == 5)
 			butterfly_lane<INV>(U, V, w, bs.rows);
-		else
+		else if constexpr (!ALL5)
 			uniform_dispatch<INV>(cls, U, V, w);
 		if (!INV && n == nline - 1) {  // last touch: the in-line layers downwards, then the compact image
 			if constexpr (swap) {
