@@ -1,119 +1,19 @@
-// b2_upper.cu -- __global__ wrapper of the upper passes (b2_upper.cuh): warp-uniform twiddles, constant
-// multiplication from shared-memory leaf masks, radix-4 blocks held in registers.  sm_100a only.
+// b2_upper.cu -- launch of the upper passes: picks the instantiation of upper_kernel (b2_upper_kernel.cuh).  sm_100a only.
 // Replaces additive_ntt_kernel<T,P> (ntt/additive_ntt.cuh:91-160) for the layers with stride >= 32 lines.
-#include <cuda_runtime.h>
-
-#include "b2_launch.h"
-#include "b2_upper.cuh"
+#include "b2_upper_kernel.cuh"
 
 namespace b2 {
-
-// Each CTA (4 warps) walks a contiguous chunk of groups, so the leaf-mask table is rebuilt only when
-// (coset row, hi) changes.  k = 4: one group (16 super-lines) per CTA at a time, two radix-4 phases
-// with one exchange through shared memory.  k = 2: one group (4 super-lines) per WARP, no exchange,
-// per-warp tables, warp-level synchronisation only.
-template <bool INV>
-__global__ void __launch_bounds__(kUpperWarps * 32, 2) upper_kernel(const __grid_constant__ UpperParams P) {
-	extern __shared__ __align__(16) uint32_t usmem_raw[];
-	UpperSmem sm = upper_smem_view(usmem_raw);
-	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-	for (int i = threadIdx.x; i < 1024; i += kUpperWarps * 32) sm.consts[i] = P.consts[i];
-	upper_rows16_fill(sm, (int)threadIdx.x, kUpperWarps * 32);
-	__syncthreads();
-	if (P.k >= 4) {
-		// The CTA works on one group of 2^k super-lines (512 lines) at a time, k / 2 layer pairs with a CTA barrier between
-		// them.  A layer pair splits the group into 2^(k-2) units of 4 super-lines; a warp runs 2^(k-4) units at once,
-		// lane = (unit of the warp) << ls | (line of the super-line).  Pair j (bits k-1-2j, k-2-2j) of unit u touches
-		// x = u_hi | a << (k-2-2j) | u_lo, a = 0..3: the low k-2-2j bits of u below the pair, the rest above.
-		const int k = P.k, ls = P.ls, upw = 1 << (k - 4), nph = k >> 1;
-		const int u = warp * upw + (lane >> ls);
-		const uint64_t per = (P.n_groups + gridDim.x - 1) / gridDim.x;
-		const uint64_t g0 = per * blockIdx.x, g1 = g0 + per < P.n_groups ? g0 + per : P.n_groups;
-		uint64_t key = ~uint64_t(0);
-#pragma unroll 1
-		for (uint64_t grp = g0; grp < g1; grp++) {
-			const UGroup c = upper_group(P, grp);
-			// every warp moves the super-lines of its own units: those of its first layer pair in, those of its last layer
-			// pair out (first pair of the forward transform: x = a << (k-2) | u; last: x = u << 2 | a), so copies need
-			// no CTA barrier and overlap other warps' logic
-			if (!INV)
-				upper_copy<false>(P, sm, c, 0, warp * upw, 1, upw, 1 << (k - 2), 4, lane);
-			else
-				upper_copy<false>(P, sm, c, 0, warp * upw * 4, 1, upw * 4, 0, 1, lane);
-			const uint64_t nk = ((uint64_t)c.row << 40) ^ c.hi;
-			if (nk != key) {  // uniform over the CTA
-				key = nk;
-				upper_twiddles(P, sm, c, (int)threadIdx.x, sm.consts);
-				__syncthreads();
-				upper_leaves(P, sm, (int)threadIdx.x, kUpperWarps * 32);
-				__syncthreads();
-			}
-			copy_wait_all();
-			__syncwarp();
-#pragma unroll 1
-			for (int e = 0; e < nph; e++) {
-				const int j = INV ? nph - 1 - e : e, b1 = k - 1 - 2 * j, b0 = b1 - 1;
-				const int xbase = ((u >> b0) << (b1 + 1)) | (u & ((1 << b0) - 1));
-				upper_pair<INV>(P, sm, lane, xbase, b0, 0, b1, e == 0, e == nph - 1);
-				if (e + 1 < nph)
-					__syncthreads();
-				else
-					__syncwarp();
-			}
-			if (!INV)
-				upper_copy<true>(P, sm, c, 0, warp * upw * 4, 1, upw * 4, 0, 1, lane);
-			else
-				upper_copy<true>(P, sm, c, 0, warp * upw, 1, upw, 1 << (k - 2), 4, lane);
-			__syncthreads();  // the slots are free again
-		}
-	} else {
-		// k = 2: one group (4 super-lines of 32 lines) per WARP, per-warp tables (3 twiddles) and slots, warp-level sync only
-		sm.leaves += warp * 3 * P.lpitch, sm.tw += warp * 4;
-		const int slot_off = warp * 4;
-		const uint64_t nw = (uint64_t)gridDim.x * kUpperWarps, wid = (uint64_t)blockIdx.x * kUpperWarps + warp;
-		const uint64_t per = (P.n_groups + nw - 1) / nw;
-		const uint64_t g0 = per * wid, g1 = g0 + per < P.n_groups ? g0 + per : P.n_groups;
-		uint64_t key = ~uint64_t(0);
-#pragma unroll 1
-		for (uint64_t grp = g0; grp < g1; grp++) {
-			const UGroup c = upper_group(P, grp);
-			upper_copy<false>(P, sm, c, slot_off, 0, 1, 4, 0, 1, lane);
-			const uint64_t nk = ((uint64_t)c.row << 40) ^ c.hi;
-			if (nk != key) {  // uniform over the warp
-				key = nk;
-				upper_twiddles(P, sm, c, lane, sm.consts);
-				__syncwarp();
-				upper_leaves(P, sm, lane, 32);
-			}
-			copy_wait_all();
-			__syncwarp();
-			upper_pair<INV>(P, sm, lane, 0, 0, slot_off, 1, true, true);
-			__syncwarp();
-			upper_copy<true>(P, sm, c, slot_off, 0, 1, 4, 0, 1, lane);
-			__syncwarp();
-		}
-	}
-}
-
-template <bool INV>
-static int launch_upper_t(const UpperParams& P, cudaStream_t stream) {
-	int sms = 0, dev = 0;
-	const size_t smem = upper_smem_words(P.k) * sizeof(uint32_t);
-	cudaGetDevice(&dev);
-	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-	cudaFuncSetAttribute(upper_kernel<INV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-	const uint64_t units = P.k >= 4 ? P.n_groups : (P.n_groups + kUpperWarps - 1) / kUpperWarps;
-	uint64_t ctas = (uint64_t)sms * 2 * 4;  // a few chunks per CTA slot for balance
-	if (ctas > units) ctas = units;
-	if (ctas == 0) return -1;
-	upper_kernel<INV><<<(unsigned)ctas, kUpperWarps * 32, smem, stream>>>(P);
-	return cudaGetLastError() == cudaSuccess ? 0 : -1;
-}
 
 int launch_upper(const UpperParams& P, cudaStream_t stream) {
 	if (P.k != 2 && P.k != 4 && P.k != 6) return -1;
 	if (P.ls != (P.k == 6 ? 3 : 5) || (P.lpitch != kLeafRows5 && P.lpitch != kLeafRows4) || (P.k == 6 && P.lpitch != kLeafRows4)) return -1;
-	return P.inverse ? launch_upper_t<true>(P, stream) : launch_upper_t<false>(P, stream);
+	// lean instantiations for passes (k >= 4) whose layers all have class 4 or all class 5
+	int cls = P.k >= 4 ? P.cls[0] : 0;
+	for (int i = 1; i < P.k && cls; i++)
+		if (P.cls[i] != cls) cls = 0;
+	if (cls != 4 && cls != 5) cls = 0;
+	if (P.inverse) return cls == 5 ? launch_upper_i5(P, stream) : cls == 4 ? launch_upper_i4(P, stream) : launch_upper_i0(P, stream);
+	return cls == 5 ? launch_upper_f5(P, stream) : cls == 4 ? launch_upper_f4(P, stream) : launch_upper_f0(P, stream);
 }
 
 }  // namespace b2

@@ -321,7 +321,7 @@ B2_HD void half_store(uint32_t* p, const uint32_t* w) {
 	for (int j = 0; j < 16; j++) p[j] = w[j];
 #endif
 }
-template <bool INV>
+template <bool INV, int CLS = 0>
 B2_HD void upper_quad_halves(const UpperParams& P, const UpperSmem& sm, int lane, int xbase, int xshift, int slot_off, int b1) {
 	const int k = P.k, ls = P.ls, l = lane & ((1 << ls) - 1);
 	uint32_t* s0 = sm.slots + ((size_t)((slot_off + xbase) << ls) + l) * kUSlotWords;
@@ -338,7 +338,16 @@ B2_HD void upper_quad_halves(const UpperParams& P, const UpperSmem& sm, int lane
 		half_load(s + sa, X1);
 		half_load(s + 2 * sa, X2);
 		half_load(s + 3 * sa, X3);
-		if (!INV) {
+		if constexpr (CLS == 4) {  // every layer of the pass has class 4: no dispatch, one circuit
+			constexpr int NI = kMatImadTerms;
+			if (!INV) {
+				butterfly_mat<4, false, NI, 16>(X0, X2, tt), butterfly_mat<4, false, NI, 16>(X1, X3, tt);
+				butterfly_mat<4, false, NI, 16>(X0, X1, t0), butterfly_mat<4, false, NI, 16>(X2, X3, t1);
+			} else {
+				butterfly_mat<4, true, NI, 16>(X0, X1, t0), butterfly_mat<4, true, NI, 16>(X2, X3, t1);
+				butterfly_mat<4, true, NI, 16>(X0, X2, tt), butterfly_mat<4, true, NI, 16>(X1, X3, tt);
+			}
+		} else if (!INV) {
 			butterfly_half_dispatch2<false>(ct, X0, X2, tt, X1, X3, tt);
 			butterfly_half_dispatch2<false>(cl, X0, X1, t0, X2, X3, t1);
 		} else {
@@ -352,15 +361,16 @@ B2_HD void upper_quad_halves(const UpperParams& P, const UpperSmem& sm, int lane
 	}
 }
 
-template <bool INV, int NT = 0>
+// CLS: 0 = the classes of the layers are read from P.cls; 4 / 5 = every layer of the pass has that class (lean instantiations)
+template <bool INV, int NT = 0, int CLS = 0>
 B2_HD void upper_pair(const UpperParams& P, const UpperSmem& sm, int lane, int xbase, int xshift, int slot_off, int b1, bool first, bool last) {
 	const int k = P.k, ls = P.ls, l = lane & ((1 << ls) - 1);  // the lane's line inside every super-line it meets
-	if (NT == 0 && P.cls[b1] <= 2 && P.cls[b1 - 1] <= 2) {
+	if (NT == 0 && CLS == 0 && P.cls[b1] <= 2 && P.cls[b1 - 1] <= 2) {
 		upper_quad_small<INV>(P, sm, lane, xbase, xshift, slot_off, b1, first, last);
 		return;
 	}
-	if (NT == 0 && P.cls[b1] <= 4 && P.cls[b1 - 1] <= 4 && !(first && !P.src_sliced) && !(last && !P.dst_sliced)) {
-		upper_quad_halves<INV>(P, sm, lane, xbase, xshift, slot_off, b1);
+	if (NT == 0 && CLS != 5 && (CLS == 4 || (P.cls[b1] <= 4 && P.cls[b1 - 1] <= 4)) && !(first && !P.src_sliced) && !(last && !P.dst_sliced)) {
+		upper_quad_halves<INV, CLS>(P, sm, lane, xbase, xshift, slot_off, b1);
 		return;
 	}
 #pragma unroll 1
@@ -385,6 +395,10 @@ B2_HD void upper_pair(const UpperParams& P, const UpperSmem& sm, int lane, int x
 				butterfly_lane_dispatch<INV>(cls, U, V, sm.tw[upper_tw_index(k, bit, xu)], sm.rows16);
 			else if (NT)
 				butterfly_lane<INV>(U, V, sm.tw[upper_tw_index(k, bit, xu)], sm.rows16);
+			else if constexpr (CLS == 5)
+				butterfly_mat<5, INV>(U, V, sm.leaves + P.lpitch * upper_tw_index(k, bit, xu));
+			else if constexpr (CLS == 4)
+				butterfly_mat<4, INV>(U, V, sm.leaves + P.lpitch * upper_tw_index(k, bit, xu));
 			else
 				butterfly_mat_dispatch<INV>(cls, U, V, sm.leaves + P.lpitch * upper_tw_index(k, bit, xu));
 			if (last && step == 1 && !P.dst_sliced) {
