@@ -22,7 +22,7 @@ __global__ void __launch_bounds__(kUpperWarps * 32, 2) upper_kernel(const __grid
 	for (int i = threadIdx.x; i < 1024; i += kUpperWarps * 32) sm.consts[i] = P.consts[i];
 	upper_rows16_fill(sm, (int)threadIdx.x, kUpperWarps * 32);
 	__syncthreads();
-	if (P.k >= 4) {
+	if (CLS != 0 || P.k >= 4) {  // the lean instantiations are launched for k >= 4 only
 		// The CTA works on one group of 2^k super-lines (512 lines) at a time, k / 2 layer pairs with a CTA barrier between
 		// them.  A layer pair splits the group into 2^(k-2) units of 4 super-lines; a warp runs 2^(k-4) units at once,
 		// lane = (unit of the warp) << ls | (line of the super-line).  Pair j (bits k-1-2j, k-2-2j) of unit u touches
@@ -68,7 +68,7 @@ __global__ void __launch_bounds__(kUpperWarps * 32, 2) upper_kernel(const __grid
 				upper_copy<true>(P, sm, c, 0, warp * upw, 1, upw, 1 << (k - 2), 4, lane);
 			__syncthreads();  // the slots are free again
 		}
-	} else {
+	} else if constexpr (CLS == 0) {
 		// k = 2: one group (4 super-lines of 32 lines) per WARP, per-warp tables (3 twiddles) and slots, warp-level sync only
 		sm.leaves += warp * 3 * P.lpitch, sm.tw += warp * 4;
 		const int slot_off = warp * 4;
